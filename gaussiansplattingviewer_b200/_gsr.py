@@ -1,0 +1,88 @@
+"""ctypes binding of csrc/libgsr.so (C ABI: include/gsr.h).  Loads the CUDA library or raises —
+there is no fallback implementation."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "csrc", "libgsr.so")
+
+GSR_FLAG_CLAMP_UNORM = 1
+GSR_FLAG_KEYS64 = 2
+GSR_FLAG_DEBUG = 4
+
+GSR_DBG_VSOUT = 0
+GSR_DBG_SETUP = 1
+GSR_DBG_INST_KEYS = 2
+GSR_DBG_INST_VALS = 3
+GSR_DBG_RANGES = 4
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("n_gaussians", C.c_longlong), ("n_visible", C.c_longlong), ("n_instances", C.c_longlong),
+        ("capacity", C.c_longlong), ("overflow", C.c_int), ("tiles_x", C.c_int), ("tiles_y", C.c_int),
+        ("ms_preprocess", C.c_float), ("ms_sort_depth", C.c_float), ("ms_duplicate", C.c_float),
+        ("ms_sort_tiles", C.c_float), ("ms_ranges", C.c_float), ("ms_blend", C.c_float), ("ms_total", C.c_float),
+    ]
+
+
+_fp = C.POINTER(C.c_float)
+_vp = C.c_void_p
+_ll = C.c_longlong
+
+# name -> (restype, argtypes); every symbol include/gsr.h declares
+SIGNATURES = {
+    "gsr_create": (C.c_int, [C.c_int, C.POINTER(_vp)]),
+    "gsr_destroy": (C.c_int, [_vp]),
+    "gsr_last_error": (C.c_char_p, []),
+    "gsr_version": (C.c_int, []),
+    "gsr_set_gaussians": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int]),
+    "gsr_set_resolution": (C.c_int, [_vp, C.c_int, C.c_int]),
+    "gsr_set_camera": (C.c_int, [_vp, _fp, _fp, _fp, C.c_float, C.c_float, C.c_float]),
+    "gsr_set_params": (C.c_int, [_vp, C.c_float, C.c_int, C.c_uint]),
+    "gsr_set_capacity": (C.c_int, [_vp, _ll]),
+    "gsr_render": (C.c_int, [_vp, _vp, _vp]),
+    "gsr_render_timed": (C.c_int, [_vp, _vp, _vp]),
+    "gsr_render_host": (C.c_int, [_vp, _vp, _vp]),
+    "gsr_render_rgb8_host": (C.c_int, [_vp, _vp, _vp]),
+    "gsr_render_r32f_host": (C.c_int, [_vp, _vp, _vp]),
+    "gsr_render_batch": (C.c_int, [_vp, _fp, _fp, C.c_int, _vp, _vp]),
+    "gsr_sort_depth": (C.c_int, [_vp, _fp, _vp, C.c_int, _vp]),
+    "gsr_sort_pairs": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int, _vp]),
+    "gsr_get_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
+    "gsr_debug_fetch": (C.c_int, [_vp, C.c_int, _vp, _ll, C.POINTER(_ll)]),
+    "gsr_scene_buffer": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_ll)]),
+    "gsr_alloc_gaussians": (C.c_int, [_vp, _ll, C.c_int]),
+    "gsr_launch_count": (_ll, [_vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Returns the loaded library; raises RuntimeError if libgsr.so is missing or does not export the ABI."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -m gaussiansplattingviewer_b200.build` "
+            "(the renderer has no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as e:
+            raise RuntimeError(f"libgsr.so does not export {name}") from e
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = load().gsr_last_error()
+        raise RuntimeError(f"gsr error {rc}: {msg.decode() if msg else ''}")

@@ -1,0 +1,604 @@
+// C ABI of libgsr.so (include/gsr.h): resource management and the per-frame launch sequence
+//   K0 set params -> K1 preprocess -> K3 depth sort (N pairs) -> K2 duplicate (depth order) ->
+//   K3 tile sort (D pairs, tile bits only) -> K4 ranges -> K5 blend
+// The two-level sort is an LSB radix sort of the 64-bit key (tile << 32 | depth bits) whose four
+// depth-digit passes run on the N Gaussians BEFORE duplication instead of on the D instances after it:
+// duplication preserves order and each Gaussian appears at most once per tile, so the final order is
+// exactly the stable order by (tile, depth, index).  GSR_FLAG_KEYS64 selects the one-sort variant.
+// No host synchronisation inside a frame: D lives on the device, buffers are capacity-bounded.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/gsr.h"
+#include "gsr_internal.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+
+#define CK(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess)                                                                       \
+            return fail(e_ == cudaErrorMemoryAllocation ? GSR_ENOMEM : GSR_ECUDA,                   \
+                        std::string(#call) + ": " + cudaGetErrorString(e_));                        \
+    } while (0)
+
+constexpr long long MAX_CAPACITY = (1ll << 30) - 1;
+
+template <typename T>
+void dfree(T*& p) {
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+}  // namespace
+
+struct gsr_renderer {
+    int device = 0;
+    long long N = 0;
+    int sh_dim = 0;
+    // resident scene (SoA)
+    float* d_xyz = nullptr;
+    float4* d_rot = nullptr;
+    float4* d_scale_op = nullptr;
+    float* d_sh = nullptr;
+    // per-Gaussian frame buffers
+    SplatBuffers sp = {};
+    uint32_t* d_dkey[2] = {nullptr, nullptr};  // depth-sort key ping-pong
+    uint32_t* d_gid[2] = {nullptr, nullptr};   // depth-sort value ping-pong
+    void* d_sortn = nullptr;                   // sort scratch sized for N
+    SortScratch ss_n = {};
+    unsigned long long* d_chain = nullptr;     // duplicate: look-back words per chunk + ticket
+    size_t chain_bytes = 0;
+    // per-instance buffers
+    long long capacity = 0, capacity_req = 0;
+    bool cap_keys64 = false;
+    void* d_ikeys[2] = {nullptr, nullptr};
+    uint32_t* d_ivals[2] = {nullptr, nullptr};
+    void* d_sorti = nullptr;
+    SortScratch ss_i = {};
+    uint64_t* d_dbgkeys = nullptr;
+    // image-side
+    int W = 0, H = 0, tiles_x = 0, tiles_y = 0;
+    int2* d_ranges = nullptr;
+    float* d_frame = nullptr;
+    uint8_t* d_rgb8 = nullptr;
+    float* d_r32 = nullptr;
+    // uniforms
+    FrameParams fp = {};
+    FrameParams* d_fp = nullptr;
+    FrameCounters* d_counters = nullptr;
+    FrameCounters* h_counters = nullptr;  // pinned
+    bool have_camera = false;
+    // last frame
+    int last_result_buf = 0;  // which instance ping-pong buffer holds the sorted list
+    bool last_keys64 = false;
+    bool frame_valid = false;
+    gsr_stats stats = {};
+    cudaEvent_t ev[8] = {};
+    long long launches = 0;
+    // scratch for gsr_sort_pairs
+    void* d_sortp = nullptr;
+    long long sortp_items = 0;
+    int sortp_keybytes = 0;
+};
+
+namespace {
+
+int free_gaussian_buffers(gsr_t* h) {
+    dfree(h->d_xyz); dfree(h->d_rot); dfree(h->d_scale_op); dfree(h->d_sh);
+    dfree(h->sp.rec0); dfree(h->sp.rec1); dfree(h->sp.rec2); dfree(h->sp.depth_key); dfree(h->sp.tiles);
+    dfree(h->sp.dbg_vsout); dfree(h->sp.dbg_setup);
+    dfree(h->d_dkey[0]); dfree(h->d_dkey[1]); dfree(h->d_gid[0]); dfree(h->d_gid[1]);
+    dfree(h->d_sortn); dfree(h->d_chain);
+    h->N = 0;
+    return 0;
+}
+
+int free_instance_buffers(gsr_t* h) {
+    dfree(h->d_ikeys[0]); dfree(h->d_ikeys[1]); dfree(h->d_ivals[0]); dfree(h->d_ivals[1]);
+    dfree(h->d_sorti); dfree(h->d_dbgkeys);
+    h->capacity = 0;
+    return 0;
+}
+
+int alloc_gaussian_buffers(gsr_t* h, long long n, int sh_dim) {
+    free_gaussian_buffers(h);
+    const size_t n1 = (size_t)std::max<long long>(n, 1);
+    CK(cudaMalloc(&h->d_xyz, n1 * 3 * sizeof(float)));
+    CK(cudaMalloc(&h->d_rot, n1 * sizeof(float4)));
+    CK(cudaMalloc(&h->d_scale_op, n1 * sizeof(float4)));
+    CK(cudaMalloc(&h->d_sh, n1 * (size_t)sh_dim * sizeof(float)));
+    CK(cudaMalloc(&h->sp.rec0, n1 * sizeof(float4)));
+    CK(cudaMalloc(&h->sp.rec1, n1 * sizeof(float4)));
+    CK(cudaMalloc(&h->sp.rec2, n1 * sizeof(float4)));
+    CK(cudaMalloc(&h->sp.depth_key, n1 * 4));
+    CK(cudaMalloc(&h->sp.tiles, n1 * 4));
+    for (int i = 0; i < 2; ++i) {
+        CK(cudaMalloc(&h->d_dkey[i], n1 * 4));
+        CK(cudaMalloc(&h->d_gid[i], n1 * 4));
+    }
+    CK(cudaMalloc(&h->d_sortn, sort_scratch_bytes((long long)n1, 4)));
+    sort_scratch_carve(&h->ss_n, h->d_sortn, (long long)n1, 4);
+    h->chain_bytes = ((n1 + 1023) / 1024 + 2) * 8;
+    CK(cudaMalloc(&h->d_chain, h->chain_bytes));
+    h->N = n;
+    h->sh_dim = sh_dim;
+    h->frame_valid = false;
+    return 0;
+}
+
+int ensure_debug_buffers(gsr_t* h) {
+    const size_t n1 = (size_t)std::max<long long>(h->N, 1);
+    if (h->fp.flags & GSR_FLAG_DEBUG) {
+        if (!h->sp.dbg_vsout) CK(cudaMalloc(&h->sp.dbg_vsout, n1 * 16 * sizeof(float)));
+        if (!h->sp.dbg_setup) CK(cudaMalloc(&h->sp.dbg_setup, n1 * 8 * sizeof(int)));
+    } else {
+        dfree(h->sp.dbg_vsout);
+        dfree(h->sp.dbg_setup);
+    }
+    return 0;
+}
+
+int ensure_capacity(gsr_t* h, long long want, bool keys64) {
+    want = std::min(std::max<long long>(want, 1024), MAX_CAPACITY);
+    if (h->capacity >= want && (h->cap_keys64 || !keys64)) return 0;
+    CK(cudaDeviceSynchronize());
+    keys64 = keys64 || h->cap_keys64;
+    free_instance_buffers(h);
+    const size_t kb = keys64 ? 8 : 4;
+    for (int i = 0; i < 2; ++i) {
+        CK(cudaMalloc(&h->d_ikeys[i], (size_t)want * kb));
+        CK(cudaMalloc(&h->d_ivals[i], (size_t)want * 4));
+    }
+    CK(cudaMalloc(&h->d_sorti, sort_scratch_bytes(want, (int)kb)));
+    sort_scratch_carve(&h->ss_i, h->d_sorti, want, (int)kb);
+    h->capacity = want;
+    h->cap_keys64 = keys64;
+    h->frame_valid = false;
+    return 0;
+}
+
+long long auto_capacity(const gsr_t* h) {
+    if (h->capacity_req > 0) return h->capacity_req;
+    return std::min<long long>(std::max<long long>(4ll << 20, 16 * h->N), MAX_CAPACITY);
+}
+
+int tile_bits(int n_tiles) {
+    int b = 1;
+    while ((1ll << b) < n_tiles) ++b;
+    return b;
+}
+
+// Enqueues one frame.  timed: record events between stages (h->ev[0..6]).
+int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bool timed) {
+    if (h->N <= 0 && !h->d_xyz) return fail(GSR_EINVAL, "no gaussians set");
+    if (h->W <= 0) return fail(GSR_EINVAL, "no resolution set");
+    if (!h->have_camera) return fail(GSR_EINVAL, "no camera set");
+    if (!out) return fail(GSR_EINVAL, "null output");
+    const bool keys64 = (fp.flags & GSR_FLAG_KEYS64) != 0;
+    int rc = ensure_debug_buffers(h);
+    if (rc) return rc;
+    rc = ensure_capacity(h, std::max(h->capacity, auto_capacity(h)), keys64);
+    if (rc) return rc;
+    const long long N = h->N, cap = h->capacity;
+    const int n_tiles = h->tiles_x * h->tiles_y;
+    const int tbits = tile_bits(n_tiles);
+    SceneBuffers scene = {h->d_xyz, h->d_rot, h->d_scale_op, h->d_sh};
+    const uint32_t* n_inst = &h->d_counters->n_instances;
+
+    if (timed) cudaEventRecord(h->ev[0], s);
+    launch_set_params(h->d_fp, fp, h->d_counters, s);
+    launch_preprocess(h->d_fp, scene, h->sp, h->d_counters, N, h->sh_dim, s);
+    h->launches += 2;
+    if (timed) cudaEventRecord(h->ev[1], s);
+    CK(cudaMemsetAsync(h->d_chain, 0, h->chain_bytes, s));
+    uint32_t* chain_ticket = reinterpret_cast<uint32_t*>(h->d_chain + (h->chain_bytes / 8 - 1));
+    int res = 0;
+    if (!keys64) {
+        // depth sort of the N Gaussians (culled ones carry key 0xFFFFFFFF and sort to the end)
+        const int r0 = radix_sort_pairs<uint32_t>(h->sp.depth_key, h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1],
+                                                  true, N, nullptr, N, 0, 32, &h->ss_n, s, &h->launches);
+        const uint32_t* sorted_gid = h->d_gid[r0];
+        if (timed) cudaEventRecord(h->ev[2], s);
+        launch_duplicate_sorted(h->d_fp, sorted_gid, h->sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain),
+                                chain_ticket, (uint32_t*)h->d_ikeys[0], h->d_ivals[0], nullptr, N, cap, s);
+        h->launches += 1;
+        if (timed) cudaEventRecord(h->ev[3], s);
+        res = radix_sort_pairs<uint32_t>((uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[1],
+                                         h->d_ivals[0], h->d_ivals[1], false, 0, n_inst, cap, 0, tbits, &h->ss_i, s,
+                                         &h->launches);
+        if (timed) cudaEventRecord(h->ev[4], s);
+        launch_tile_ranges<uint32_t>((const uint32_t*)h->d_ikeys[res], 0, h->d_counters, cap, h->d_ranges, n_tiles, s);
+    } else {
+        if (timed) cudaEventRecord(h->ev[2], s);
+        launch_duplicate_keys64(h->d_fp, h->sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain), chain_ticket,
+                                (uint64_t*)h->d_ikeys[0], h->d_ivals[0], N, cap, s);
+        h->launches += 1;
+        if (timed) cudaEventRecord(h->ev[3], s);
+        res = radix_sort_pairs<uint64_t>((uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[1],
+                                         h->d_ivals[0], h->d_ivals[1], false, 0, n_inst, cap, 0, 32 + tbits, &h->ss_i, s,
+                                         &h->launches);
+        if (timed) cudaEventRecord(h->ev[4], s);
+        launch_tile_ranges<uint64_t>((const uint64_t*)h->d_ikeys[res], 32, h->d_counters, cap, h->d_ranges, n_tiles, s);
+    }
+    h->launches += 1;
+    if (timed) cudaEventRecord(h->ev[5], s);
+    launch_blend(h->d_fp, h->d_ranges, h->d_ivals[res], h->sp, out, fp.render_mod, fp.flags, h->tiles_x, h->tiles_y, s);
+    h->launches += 1;
+    if (timed) cudaEventRecord(h->ev[6], s);
+    CK(cudaMemcpyAsync(h->h_counters, h->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, s));
+    h->last_result_buf = res;
+    h->last_keys64 = keys64;
+    h->frame_valid = true;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// render + (optional conversion) + D2H, growing the instance buffers on overflow
+int render_to_host(gsr_t* h, void* host_dst, int kind /*0 rgba f32, 1 rgb8, 2 r32f*/, cudaStream_t s) {
+    if (!host_dst) return fail(GSR_EINVAL, "null output");
+    const long long npx = (long long)h->W * h->H;
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        int rc = render_frame(h, h->fp, h->d_frame, s, false);
+        if (rc) return rc;
+        if (kind == 0) {
+            CK(cudaMemcpyAsync(host_dst, h->d_frame, (size_t)npx * 16, cudaMemcpyDeviceToHost, s));
+        } else if (kind == 1) {
+            launch_pack_rgb8(h->d_frame, h->d_rgb8, npx, s);
+            h->launches += 1;
+            CK(cudaMemcpyAsync(host_dst, h->d_rgb8, (size_t)npx * 3, cudaMemcpyDeviceToHost, s));
+        } else {
+            launch_extract_r(h->d_frame, h->d_r32, npx, s);
+            h->launches += 1;
+            CK(cudaMemcpyAsync(host_dst, h->d_r32, (size_t)npx * 4, cudaMemcpyDeviceToHost, s));
+        }
+        CK(cudaStreamSynchronize(s));
+        if (!h->h_counters->overflow) return 0;
+        const long long d = h->h_counters->n_instances;
+        if (h->capacity >= MAX_CAPACITY) break;
+        long long want = std::max(h->capacity * 2, d + d / 8);
+        h->capacity_req = 0;
+        rc = ensure_capacity(h, want, h->cap_keys64);
+        if (rc) return rc;
+    }
+    return fail(GSR_EOVERFLOW, "tile-instance buffer overflow");
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* gsr_last_error(void) { return g_err.c_str(); }
+int gsr_version(void) { return 100; }
+
+int gsr_create(int device, gsr_t** out) {
+    if (!out) return fail(GSR_EINVAL, "null out");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0)
+        return fail(GSR_ECUDA, std::string("no CUDA device: ") + cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(GSR_EINVAL, "bad device index");
+    CK(cudaSetDevice(device));
+    gsr_t* h = new gsr_renderer();
+    h->device = device;
+    CK(cudaMalloc(&h->d_fp, sizeof(FrameParams) * 2));
+    CK(cudaMalloc(&h->d_counters, sizeof(FrameCounters)));
+    CK(cudaMemset(h->d_counters, 0, sizeof(FrameCounters)));
+    CK(cudaMallocHost(&h->h_counters, sizeof(FrameCounters)));
+    memset(h->h_counters, 0, sizeof(FrameCounters));
+    for (auto& ev : h->ev) CK(cudaEventCreate(&ev));
+    h->fp.scale_modifier = 1.f;
+    h->fp.render_mod = 3;
+    h->fp.flags = GSR_FLAG_CLAMP_UNORM;
+    *out = h;
+    return 0;
+}
+
+int gsr_destroy(gsr_t* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    free_gaussian_buffers(h);
+    free_instance_buffers(h);
+    dfree(h->d_ranges); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
+    dfree(h->d_fp); dfree(h->d_counters); dfree(h->d_sortp);
+    if (h->h_counters) cudaFreeHost(h->h_counters);
+    for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+    delete h;
+    return 0;
+}
+
+int gsr_alloc_gaussians(gsr_t* h, long long n, int sh_dim) {
+    if (!h || n < 0 || sh_dim < 3 || sh_dim > 48 || sh_dim % 3) return fail(GSR_EINVAL, "bad n / sh_dim");
+    if (n >= (1ll << 31) - 1024) return fail(GSR_EINVAL, "too many gaussians");
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    int rc = alloc_gaussian_buffers(h, n, sh_dim);
+    if (rc) return rc;
+    h->fp.sh_dim = sh_dim;
+    return 0;
+}
+
+int gsr_set_gaussians(gsr_t* h, const float* xyz, const float* rot, const float* scale, const float* opacity,
+                      const float* sh, long long n, int sh_dim, int src_is_device) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    if (n > 0 && (!xyz || !rot || !scale || !opacity || !sh)) return fail(GSR_EINVAL, "null array");
+    int rc = gsr_alloc_gaussians(h, n, sh_dim);
+    if (rc) return rc;
+    if (n == 0) return 0;
+    const cudaMemcpyKind kind = src_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    const size_t n1 = (size_t)n;
+    CK(cudaMemcpy(h->d_xyz, xyz, n1 * 12, kind));
+    CK(cudaMemcpy(h->d_sh, sh, n1 * (size_t)sh_dim * 4, kind));
+    // rot / scale / opacity are packed into two float4 planes on the device
+    float *t_rot = nullptr, *t_scale = nullptr, *t_op = nullptr;
+    const float *p_rot = rot, *p_scale = scale, *p_op = opacity;
+    if (!src_is_device) {
+        CK(cudaMalloc(&t_rot, n1 * 16)); CK(cudaMalloc(&t_scale, n1 * 12)); CK(cudaMalloc(&t_op, n1 * 4));
+        CK(cudaMemcpy(t_rot, rot, n1 * 16, kind));
+        CK(cudaMemcpy(t_scale, scale, n1 * 12, kind));
+        CK(cudaMemcpy(t_op, opacity, n1 * 4, kind));
+        p_rot = t_rot; p_scale = t_scale; p_op = t_op;
+    }
+    launch_pack_scene(p_rot, p_scale, p_op, h->d_rot, h->d_scale_op, n, 0);
+    h->launches += 1;
+    CK(cudaDeviceSynchronize());
+    if (t_rot) { cudaFree(t_rot); cudaFree(t_scale); cudaFree(t_op); }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int gsr_scene_buffer(gsr_t* h, int which, void** dev_ptr, long long* bytes) {
+    if (!h || !dev_ptr || !bytes) return fail(GSR_EINVAL, "null argument");
+    const long long n = h->N;
+    switch (which) {
+        case 0: *dev_ptr = h->d_xyz; *bytes = n * 12; break;
+        case 1: *dev_ptr = h->d_rot; *bytes = n * 16; break;
+        case 2: *dev_ptr = h->d_scale_op; *bytes = n * 16; break;
+        case 3: *dev_ptr = h->d_sh; *bytes = n * (long long)h->sh_dim * 4; break;
+        default: return fail(GSR_EINVAL, "bad buffer selector");
+    }
+    return 0;
+}
+
+int gsr_set_resolution(gsr_t* h, int width, int height) {
+    if (!h || width <= 0 || height <= 0 || width > 65535 || height > 65535) return fail(GSR_EINVAL, "bad resolution");
+    CK(cudaSetDevice(h->device));
+    if (width == h->W && height == h->H) return 0;
+    CK(cudaDeviceSynchronize());
+    dfree(h->d_ranges); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
+    h->W = width; h->H = height;
+    h->tiles_x = (width + GSR_TILE - 1) / GSR_TILE;
+    h->tiles_y = (height + GSR_TILE - 1) / GSR_TILE;
+    const size_t npx = (size_t)width * height;
+    CK(cudaMalloc(&h->d_ranges, sizeof(int2) * (size_t)h->tiles_x * h->tiles_y));
+    CK(cudaMalloc(&h->d_frame, npx * 16));
+    CK(cudaMalloc(&h->d_rgb8, npx * 3));
+    CK(cudaMalloc(&h->d_r32, npx * 4));
+    h->fp.W = width; h->fp.H = height; h->fp.tiles_x = h->tiles_x; h->fp.tiles_y = h->tiles_y;
+    h->frame_valid = false;
+    return 0;
+}
+
+int gsr_set_camera(gsr_t* h, const float view[16], const float proj[16], const float campos[3], float htanx,
+                   float htany, float focal) {
+    if (!h || !view || !proj || !campos) return fail(GSR_EINVAL, "null argument");
+    memcpy(h->fp.view, view, 64);
+    memcpy(h->fp.proj, proj, 64);
+    memcpy(h->fp.campos, campos, 12);
+    h->fp.htanx = htanx; h->fp.htany = htany; h->fp.focal = focal;
+    h->have_camera = true;
+    return 0;
+}
+
+int gsr_set_params(gsr_t* h, float scale_modifier, int render_mod, unsigned flags) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    if (render_mod < -4) return fail(GSR_EINVAL, "render_mod must be >= -4");
+    h->fp.scale_modifier = scale_modifier;
+    h->fp.render_mod = render_mod;
+    h->fp.flags = flags;
+    return 0;
+}
+
+int gsr_set_capacity(gsr_t* h, long long max_instances) {
+    if (!h || max_instances < 0 || max_instances > MAX_CAPACITY) return fail(GSR_EINVAL, "bad capacity");
+    CK(cudaSetDevice(h->device));
+    h->capacity_req = max_instances;
+    if (max_instances > 0 && max_instances != h->capacity) {
+        CK(cudaDeviceSynchronize());
+        const bool k64 = h->cap_keys64;
+        free_instance_buffers(h);
+        h->cap_keys64 = false;
+        return ensure_capacity(h, max_instances, k64);
+    }
+    return 0;
+}
+
+int gsr_render(gsr_t* h, float* out_rgba, void* stream) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    CK(cudaSetDevice(h->device));
+    h->fp.sh_dim = h->sh_dim;
+    return render_frame(h, h->fp, out_rgba, (cudaStream_t)stream, false);
+}
+
+int gsr_render_timed(gsr_t* h, float* out_rgba, void* stream) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    CK(cudaSetDevice(h->device));
+    h->fp.sh_dim = h->sh_dim;
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = render_frame(h, h->fp, out_rgba, s, true);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(s));
+    float ms[6];
+    for (int i = 0; i < 6; ++i) CK(cudaEventElapsedTime(&ms[i], h->ev[i], h->ev[i + 1]));
+    h->stats.ms_preprocess = ms[0];
+    h->stats.ms_sort_depth = ms[1];
+    h->stats.ms_duplicate = ms[2];
+    h->stats.ms_sort_tiles = ms[3];
+    h->stats.ms_ranges = ms[4];
+    h->stats.ms_blend = ms[5];
+    CK(cudaEventElapsedTime(&h->stats.ms_total, h->ev[0], h->ev[6]));
+    return 0;
+}
+
+int gsr_render_host(gsr_t* h, float* out, void* stream) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    CK(cudaSetDevice(h->device));
+    h->fp.sh_dim = h->sh_dim;
+    return render_to_host(h, out, 0, (cudaStream_t)stream);
+}
+int gsr_render_rgb8_host(gsr_t* h, uint8_t* out, void* stream) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    CK(cudaSetDevice(h->device));
+    h->fp.sh_dim = h->sh_dim;
+    return render_to_host(h, out, 1, (cudaStream_t)stream);
+}
+int gsr_render_r32f_host(gsr_t* h, float* out, void* stream) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    CK(cudaSetDevice(h->device));
+    h->fp.sh_dim = h->sh_dim;
+    return render_to_host(h, out, 2, (cudaStream_t)stream);
+}
+
+int gsr_render_batch(gsr_t* h, const float* views, const float* campos, int n_views, float* out_rgba, void* stream) {
+    if (!h || !views || !campos || n_views < 0) return fail(GSR_EINVAL, "bad argument");
+    CK(cudaSetDevice(h->device));
+    if (!h->have_camera) return fail(GSR_EINVAL, "set intrinsics with gsr_set_camera first");
+    h->fp.sh_dim = h->sh_dim;
+    const size_t frame = (size_t)h->W * h->H * 4;
+    FrameParams fp = h->fp;
+    for (int v = 0; v < n_views; ++v) {
+        memcpy(fp.view, views + 16 * (size_t)v, 64);
+        memcpy(fp.campos, campos + 3 * (size_t)v, 12);
+        float* dst = out_rgba ? out_rgba + frame * (size_t)v : h->d_frame;
+        int rc = render_frame(h, fp, dst, (cudaStream_t)stream, false);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_is_device, void* stream) {
+    if (!h || !view || !out_index) return fail(GSR_EINVAL, "null argument");
+    if (!h->d_xyz) return fail(GSR_EINVAL, "no gaussians set");
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long N = h->N;
+    if (N == 0) return 0;
+    launch_depth_keys(h->d_xyz, view, h->d_dkey[0], N, s);
+    h->launches += 1;
+    const int r = radix_sort_pairs<uint32_t>(h->d_dkey[0], h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1], true, N,
+                                             nullptr, N, 0, 32, &h->ss_n, s, &h->launches);
+    CK(cudaMemcpyAsync(out_index, h->d_gid[r], (size_t)N * 4,
+                       dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+    if (!dst_is_device) CK(cudaStreamSynchronize(s));
+    h->frame_valid = false;
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int gsr_sort_pairs(gsr_t* h, int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, long long n,
+                   int begin_bit, int end_bit, void* stream) {
+    if (!h || !keys || !keys_tmp || !vals_tmp) return fail(GSR_EINVAL, "null argument");
+    if (key_bits != 32 && key_bits != 64) return fail(GSR_EINVAL, "key_bits must be 32 or 64");
+    if (begin_bit < 0 || end_bit > key_bits || begin_bit > end_bit) return fail(GSR_EINVAL, "bad bit range");
+    if (n < 0 || n > MAX_CAPACITY) return fail(GSR_EINVAL, "bad n");
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n == 0 || begin_bit == end_bit) return 0;
+    const int kb = key_bits / 8;
+    if (h->sortp_items < n || h->sortp_keybytes != kb) {
+        CK(cudaDeviceSynchronize());
+        dfree(h->d_sortp);
+        CK(cudaMalloc(&h->d_sortp, sort_scratch_bytes(n, kb)));
+        h->sortp_items = n;
+        h->sortp_keybytes = kb;
+    }
+    SortScratch ss;
+    sort_scratch_carve(&ss, h->d_sortp, h->sortp_items, kb);
+    const bool identity = (vals == nullptr);
+    uint32_t* vals_a = vals;
+    int r;
+    if (identity) {
+        // results must land somewhere: with identity input the caller passes the OUTPUT buffer as vals_tmp
+        // and we need a second value buffer for the ping-pong; borrow it from the key scratch size class
+        return fail(GSR_EINVAL, "vals == NULL (identity) is only supported through gsr_sort_depth");
+    }
+    if (kb == 4)
+        r = radix_sort_pairs<uint32_t>((uint32_t*)keys, (uint32_t*)keys, (uint32_t*)keys_tmp, vals_a, vals_tmp, false, n,
+                                       nullptr, n, begin_bit, end_bit, &ss, s, &h->launches);
+    else
+        r = radix_sort_pairs<uint64_t>((uint64_t*)keys, (uint64_t*)keys, (uint64_t*)keys_tmp, vals_a, vals_tmp, false, n,
+                                       nullptr, n, begin_bit, end_bit, &ss, s, &h->launches);
+    if (r == 1) {  // odd number of passes: bring the result back to keys / vals
+        CK(cudaMemcpyAsync(keys, keys_tmp, (size_t)n * kb, cudaMemcpyDeviceToDevice, s));
+        CK(cudaMemcpyAsync(vals, vals_tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int gsr_get_stats(gsr_t* h, gsr_stats* out) {
+    if (!h || !out) return fail(GSR_EINVAL, "null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    h->stats.n_gaussians = h->N;
+    h->stats.n_visible = h->h_counters->n_visible;
+    h->stats.n_instances = h->h_counters->n_instances;
+    h->stats.overflow = (int)h->h_counters->overflow;
+    h->stats.capacity = h->capacity;
+    h->stats.tiles_x = h->tiles_x;
+    h->stats.tiles_y = h->tiles_y;
+    *out = h->stats;
+    return 0;
+}
+
+int gsr_debug_fetch(gsr_t* h, int which, void* dst, long long capacity_bytes, long long* out_bytes) {
+    if (!h || !out_bytes) return fail(GSR_EINVAL, "null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    if (!h->frame_valid) return fail(GSR_EINVAL, "no frame rendered since the last state change");
+    const long long D = std::min<long long>(h->h_counters->n_instances, h->capacity);
+    const void* src = nullptr;
+    long long bytes = 0;
+    switch (which) {
+        case GSR_DBG_VSOUT:
+            if (!h->sp.dbg_vsout) return fail(GSR_EINVAL, "GSR_FLAG_DEBUG was not set for the last frame");
+            src = h->sp.dbg_vsout; bytes = h->N * 64; break;
+        case GSR_DBG_SETUP:
+            if (!h->sp.dbg_setup) return fail(GSR_EINVAL, "GSR_FLAG_DEBUG was not set for the last frame");
+            src = h->sp.dbg_setup; bytes = h->N * 32; break;
+        case GSR_DBG_INST_KEYS:
+            bytes = D * 8;
+            if (h->last_keys64) src = h->d_ikeys[h->last_result_buf];
+            else if (D > 0 && dst) {
+                dfree(h->d_dbgkeys);
+                CK(cudaMalloc(&h->d_dbgkeys, (size_t)D * 8));
+                launch_keys64_from_sorted((const uint32_t*)h->d_ikeys[h->last_result_buf], h->d_ivals[h->last_result_buf],
+                                          h->sp.depth_key, h->d_counters, h->capacity, h->d_dbgkeys, 0);
+                CK(cudaDeviceSynchronize());
+                src = h->d_dbgkeys;
+            }
+            break;
+        case GSR_DBG_INST_VALS: src = h->d_ivals[h->last_result_buf]; bytes = D * 4; break;
+        case GSR_DBG_RANGES: src = h->d_ranges; bytes = (long long)h->tiles_x * h->tiles_y * 8; break;
+        default: return fail(GSR_EINVAL, "bad selector");
+    }
+    *out_bytes = bytes;
+    if (!dst) return 0;
+    if (capacity_bytes < bytes) return fail(GSR_EINVAL, "destination too small");
+    if (bytes > 0 && src) CK(cudaMemcpy(dst, src, (size_t)bytes, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+long long gsr_launch_count(gsr_t* h) { return h ? h->launches : 0; }
+
+}  // extern "C"

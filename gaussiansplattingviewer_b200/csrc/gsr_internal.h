@@ -1,0 +1,98 @@
+// Internal declarations shared by the CUDA translation units of libgsr.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GSR_TILE 16  // pixels per tile edge (16x16 tiles, one CTA per tile in the blend kernel)
+
+// Per-frame uniforms.  Lives in device memory (written by k_set_params) so that a captured CUDA graph
+// can be replayed with a new camera by updating one kernel node.
+struct FrameParams {
+    float view[16];  // row-major maths layout
+    float proj[16];
+    float htanx, htany, focal;
+    float campos[3];
+    float scale_modifier;
+    int render_mod;
+    int sh_dim;
+    int W, H;
+    int tiles_x, tiles_y;
+    unsigned flags;
+};
+
+// Device-side counters of one frame (zeroed at frame start).
+struct FrameCounters {
+    unsigned n_visible;    // Gaussians with ok = 1
+    unsigned n_instances;  // D (sum of tiles touched), unclamped
+    unsigned overflow;     // D > capacity
+    unsigned pad;
+};
+
+// Splat record, three float4 planes indexed by Gaussian:
+//   rec0 = (cx, cy, bits(imin | (imax-imin) << 16), bits(jmin | (jmax-jmin) << 16))
+//   rec1 = (conic A, conic B, conic C, opacity)
+//   rec2 = (r, g, b, depth)
+struct SceneBuffers {
+    const float* xyz;      // N x 3
+    const float4* rot;     // N (w, x, y, z)
+    const float4* scale_op;  // N (sx, sy, sz, opacity)
+    const float* sh;       // N x sh_dim
+};
+
+struct SplatBuffers {
+    float4* rec0;
+    float4* rec1;
+    float4* rec2;
+    uint32_t* depth_key;  // bits(depth) or 0xFFFFFFFF when not ok
+    uint32_t* tiles;      // tiles touched (0 when not ok)
+    float* dbg_vsout;     // N x 16 or nullptr
+    int32_t* dbg_setup;   // N x 8 or nullptr
+};
+
+// ---- radix sort (radix_sort.cu) ----------------------------------------------------------------
+// Scratch for one sort: histograms for up to 8 passes, ticket counters, two look-back status buffers.
+struct SortScratch {
+    uint32_t* hist;       // [8][256] raw digit counts per pass
+    uint32_t* tickets;    // [8] tile tickets per pass (+ 1 for the histogram kernel)
+    uint32_t* status[2];  // [max_tiles][256] decoupled look-back words, alternating per pass
+    long long max_tiles;
+    size_t zero_bytes;    // bytes to clear at sort start (hist + tickets are contiguous)
+};
+size_t sort_scratch_bytes(long long max_items, int key_bytes);
+void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key_bytes);
+
+// Sorts n pairs (n read from *n_dev when n_dev != nullptr, else n_host) on bits [begin_bit, end_bit).
+// keys/vals are ping-ponged with keys_tmp/vals_tmp; the number of passes is made even by the caller or
+// the result location is returned: returns 0 if the result is in keys/vals, 1 if in keys_tmp/vals_tmp.
+// vals_in may be nullptr (identity).  hist_ready: the per-pass histograms were already accumulated into
+// scratch->hist by a producer kernel (skip the histogram kernel and the clear).
+// keys_first: input of the first pass (may equal keys; it is only read), so a key array can be sorted
+// without being overwritten.
+template <typename KeyT>
+int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
+                     long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
+                     SortScratch* scratch, cudaStream_t stream, long long* launch_count);
+
+// ---- kernels' host launchers ---------------------------------------------------------------------
+void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s);
+void launch_pack_scene(const float* rot, const float* scale, const float* opacity, float4* rot4, float4* scale_op,
+                       long long n, cudaStream_t s);
+void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
+                       long long n, int sh_dim, cudaStream_t s);
+void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s);
+void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, SplatBuffers sp,
+                             FrameCounters* counters, uint32_t* chain_status, uint32_t* chain_ticket,
+                             uint32_t* out_tile, uint32_t* out_gid, uint32_t* tile_hist /* [2][256] or nullptr */,
+                             long long n, long long capacity, cudaStream_t s);
+void launch_duplicate_keys64(const FrameParams* fp, SplatBuffers sp, FrameCounters* counters, uint32_t* chain_status,
+                             uint32_t* chain_ticket, uint64_t* out_keys, uint32_t* out_gid, long long n,
+                             long long capacity, cudaStream_t s);
+template <typename KeyT>
+void launch_tile_ranges(const KeyT* sorted_keys, int key_shift, const FrameCounters* counters, long long capacity,
+                        int2* ranges, int n_tiles, cudaStream_t s);
+void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
+                  float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s);
+void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s);
+void launch_extract_r(const float* rgba, float* r, long long n_px, cudaStream_t s);
+void launch_keys64_from_sorted(const uint32_t* tile_keys, const uint32_t* gid, const uint32_t* depth_key,
+                               const FrameCounters* counters, long long capacity, uint64_t* out, cudaStream_t s);

@@ -1,0 +1,371 @@
+// K1 — per-Gaussian preprocess for sm_100a.
+//
+// One thread per Gaussian: frustum cull, 3D covariance from scale/rotation, EWA projection to a 2D
+// conic, 3-sigma axis-aligned footprint, exact pixel/tile rectangle, SH degree 0..3 or disparity
+// colour.  Restates /root/reference/shaders/gau_vert.glsl:73-251 (per instance, once instead of once
+// per quad vertex) plus the raster set-up rules of oracle/ref_driver.inc.
+//
+// THIS FILE IS COMPILED WITH -fmad=false: every operation is a separately rounded IEEE binary32
+// operation in the order the shader writes it (conventions in oracle/glsl_shim.hpp), so the splat
+// records are bit-identical to the CPU oracle's.  The kernel is HBM-bound (12 B per culled Gaussian,
+// ~236 B in / 56 B out per visible one), so the unfused arithmetic costs nothing.
+#include "gsr_internal.h"
+
+namespace {
+
+#define SH_C0 0.28209479177387814f
+#define SH_C1 0.4886025119029199f
+#define SH_C2_0 1.0925484305920792f
+#define SH_C2_1 -1.0925484305920792f
+#define SH_C2_2 0.31539156525252005f
+#define SH_C2_3 -1.0925484305920792f
+#define SH_C2_4 0.5462742152960396f
+#define SH_C3_0 -0.5900435899266435f
+#define SH_C3_1 2.890611442640554f
+#define SH_C3_2 -0.4570457994644658f
+#define SH_C3_3 0.3731763325901154f
+#define SH_C3_4 -0.4570457994644658f
+#define SH_C3_5 1.445305721320277f
+#define SH_C3_6 -0.5900435899266435f
+
+__device__ __forceinline__ float gl_min(float x, float y) { return (y < x) ? y : x; }
+__device__ __forceinline__ float gl_max(float x, float y) { return (x < y) ? y : x; }
+
+struct m3 { float m[3][3]; };  // column-major like GLSL: m[col][row]
+
+__device__ __forceinline__ m3 m3_mul(const m3& A, const m3& B) {
+    m3 R;
+#pragma unroll
+    for (int col = 0; col < 3; ++col)
+#pragma unroll
+        for (int row = 0; row < 3; ++row)
+            R.m[col][row] = (A.m[0][row] * B.m[col][0] + A.m[1][row] * B.m[col][1]) + A.m[2][row] * B.m[col][2];
+    return R;
+}
+__device__ __forceinline__ m3 m3_transpose(const m3& A) {
+    m3 R;
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int r = 0; r < 3; ++r) R.m[c][r] = A.m[r][c];
+    return R;
+}
+__device__ __forceinline__ void mat4_mul_vec4(const float* __restrict__ M, const float v[4], float out[4]) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+        out[r] = ((M[r * 4 + 0] * v[0] + M[r * 4 + 1] * v[1]) + M[r * 4 + 2] * v[2]) + M[r * 4 + 3] * v[3];
+}
+
+// pixel coverage interval, identical to cover_lo / cover_hi in oracle/gs_oracle.c
+__device__ __forceinline__ int cover_lo(float c, float h, int n) {
+    const float f = (c - h) - 0.5f;
+    int i;
+    if (!(f > 0.f)) i = 0;
+    else if (f >= (float)n) i = n;
+    else i = (int)floorf(f);
+    while (i > 0 && (((float)(i - 1) + 0.5f) - c) >= -h) --i;
+    while (i < n && (((float)i + 0.5f) - c) < -h) ++i;
+    return i;
+}
+__device__ __forceinline__ int cover_hi(float c, float h, int n) {
+    const float g = (c + h) - 0.5f;
+    int i;
+    if (!(g >= 0.f)) i = -1;
+    else if (g >= (float)(n - 1)) i = n - 1;
+    else i = (int)floorf(g);
+    while (i < n - 1 && (((float)(i + 1) + 0.5f) - c) <= h) ++i;
+    while (i >= 0 && (((float)i + 0.5f) - c) > h) --i;
+    return i;
+}
+
+__device__ __forceinline__ bool finitef(float x) { return fabsf(x) <= 3.402823466e+38f; }
+
+// Block-uniform copy of the frame uniforms into shared memory.
+struct SharedParams {
+    float view[16];
+    float proj[16];
+    float htanx, htany, focal;
+    float campos[3];
+    float scale_modifier;
+    int render_mod, W, H, tiles_x;
+    unsigned flags;
+};
+
+template <int SH_DIM, bool DEBUG>
+__global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restrict__ fp, SceneBuffers scene,
+                                                    SplatBuffers out, FrameCounters* __restrict__ counters,
+                                                    unsigned n, int sh_dim_rt) {
+    __shared__ SharedParams P;
+    __shared__ unsigned s_visible;
+    if (threadIdx.x < 16) { P.view[threadIdx.x] = fp->view[threadIdx.x]; P.proj[threadIdx.x] = fp->proj[threadIdx.x]; }
+    if (threadIdx.x == 32) {
+        P.htanx = fp->htanx; P.htany = fp->htany; P.focal = fp->focal;
+        P.campos[0] = fp->campos[0]; P.campos[1] = fp->campos[1]; P.campos[2] = fp->campos[2];
+        P.scale_modifier = fp->scale_modifier; P.render_mod = fp->render_mod;
+        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.flags = fp->flags;
+        s_visible = 0;
+    }
+    __syncthreads();
+    const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+    bool ok = false;
+    if (g < n) {
+        const int sh_dim = (SH_DIM > 0) ? SH_DIM : sh_dim_rt;
+        const int mod = P.render_mod;
+        // ---- gau_vert.glsl:134-146: project + early cull
+        const float px = __ldg(scene.xyz + 3 * (size_t)g + 0);
+        const float py = __ldg(scene.xyz + 3 * (size_t)g + 1);
+        const float pz = __ldg(scene.xyz + 3 * (size_t)g + 2);
+        const float g_pos[4] = {px, py, pz, 1.f};
+        float pv[4], pc[4];
+        mat4_mul_vec4(P.view, g_pos, pv);
+        mat4_mul_vec4(P.proj, pv, pc);
+        const float ndc0 = pc[0] / pc[3], ndc1 = pc[1] / pc[3], ndc2 = pc[2] / pc[3];
+        const float lim = (float)1.3;
+        const bool culled = (fabsf(ndc0) > lim || fabsf(ndc1) > lim || fabsf(ndc2) > lim);
+
+        float vs[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) vs[k] = 0.f;
+        int imin = 0, imax = -1, jmin = 0, jmax = -1;
+        float cx = 0.f, cy = 0.f, depth = 0.f;
+        float conic0 = 0.f, conic1 = 0.f, conic2 = 0.f, alpha = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
+
+        if (!culled) {
+            const float4 q = __ldg(scene.rot + g);
+            const float4 so = __ldg(scene.scale_op + g);
+            depth = -pv[2];
+            const float ndcx = ndc0 + 0.f, ndcy = ndc1 + 0.f;
+            // ---- :151-156 scale, computeCov3D :73-93
+            float s[3] = {so.x * P.scale_modifier, so.y * P.scale_modifier, so.z * P.scale_modifier};
+            if (mod == -1) { s[0] = s[0] * (float)1.2; s[1] = s[1] * (float)1.2; s[2] = s[2] * (float)1.2; }
+            m3 S;
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int r = 0; r < 3; ++r) S.m[c][r] = 0.f;
+            S.m[0][0] = s[0]; S.m[1][1] = s[1]; S.m[2][2] = s[2];
+            const float r = q.x, x = q.y, y = q.z, z = q.w;
+            m3 R;
+            R.m[0][0] = 1.f - 2.f * (y * y + z * z); R.m[0][1] = 2.f * (x * y - r * z); R.m[0][2] = 2.f * (x * z + r * y);
+            R.m[1][0] = 2.f * (x * y + r * z); R.m[1][1] = 1.f - 2.f * (x * x + z * z); R.m[1][2] = 2.f * (y * z - r * x);
+            R.m[2][0] = 2.f * (x * z - r * y); R.m[2][1] = 2.f * (y * z + r * x); R.m[2][2] = 1.f - 2.f * (x * x + y * y);
+            const m3 M = m3_mul(S, R);
+            const m3 cov3d = m3_mul(m3_transpose(M), M);
+            // ---- computeCov2D :95-120
+            float tx = pv[0], ty = pv[1];
+            const float tz = pv[2];
+            const float limx = 1.3f * P.htanx, limy = 1.3f * P.htany;
+            const float txtz = tx / tz, tytz = ty / tz;
+            tx = gl_min(limx, gl_max(-limx, txtz)) * tz;
+            ty = gl_min(limy, gl_max(-limy, tytz)) * tz;
+            const float focal = P.focal;
+            m3 J;
+            J.m[0][0] = focal / tz; J.m[0][1] = 0.0f; J.m[0][2] = -(focal * tx) / (tz * tz);
+            J.m[1][0] = 0.0f; J.m[1][1] = focal / tz; J.m[1][2] = -(focal * ty) / (tz * tz);
+            J.m[2][0] = 0.f; J.m[2][1] = 0.f; J.m[2][2] = 0.f;
+            m3 Wm;
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int rr = 0; rr < 3; ++rr) Wm.m[c][rr] = P.view[c * 4 + rr];
+            const m3 T = m3_mul(Wm, J);
+            const m3 A = m3_mul(m3_transpose(T), m3_transpose(cov3d));
+            m3 cov = m3_mul(A, T);
+            cov.m[0][0] += 0.3f;
+            cov.m[1][1] += 0.3f;
+            const float ca = cov.m[0][0], cb = cov.m[0][1], cc = cov.m[1][1];
+            // ---- :167-178 conic + footprint
+            const float det = (ca * cc - cb * cb);
+            const float det_inv = 1.f / det;
+            conic0 = cc * det_inv; conic1 = -cb * det_inv; conic2 = ca * det_inv;
+            const float hx = 3.f * sqrtf(ca), hy = 3.f * sqrtf(cc);
+            alpha = so.w;
+            // ---- colour
+            if (mod == -1) {  // :182-211 disparity
+                const float baseline = -0.5f;
+                const float xl = (ndc0 + 1.f) / 2.f;
+                const float pr[4] = {px + baseline, py + 0.f, pz + 0.f, 1.f};
+                float pvr[4], pcr[4];
+                mat4_mul_vec4(P.view, pr, pvr);
+                mat4_mul_vec4(P.proj, pvr, pcr);
+                const float xr = ((pcr[0] / pcr[3]) + 1.f) / 2.f;
+                const float d = fabsf(xl - xr);
+                c0 = d; c1 = d; c2 = d;
+            } else {  // :214-250 SH
+                float dx = px - P.campos[0], dy = py - P.campos[1], dz = pz - P.campos[2];
+                const float len = sqrtf((dx * dx + dy * dy) + dz * dz);
+                dx = dx / len; dy = dy / len; dz = dz / len;
+                const float* __restrict__ shp = scene.sh + (size_t)sh_dim * (size_t)g;
+                int ncoef = 1;
+                if (sh_dim > 3 && mod >= 1) ncoef = 4;
+                if (sh_dim > 12 && mod >= 2) ncoef = 9;
+                if (sh_dim > 27 && mod >= 3) ncoef = 16;
+                float sh[48];
+                if (SH_DIM == 48) {
+                    const float4* __restrict__ sh4 = reinterpret_cast<const float4*>(shp);
+                    const int nv = (ncoef * 3 + 3) >> 2;  // float4s needed: 1, 3, 7, 12
+#pragma unroll
+                    for (int k = 0; k < 12; ++k) {
+                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (k < nv) v = __ldg(sh4 + k);
+                        sh[4 * k + 0] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 48; ++k) sh[k] = (k < ncoef * 3 && k < sh_dim) ? __ldg(shp + k) : 0.f;
+                }
+#define SHV(k, ch) sh[(k) * 3 + (ch)]
+                float c[3];
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) c[ch] = SH_C0 * SHV(0, ch);
+                if (ncoef >= 4) {
+                    const float X = dx, Y = dy, Z = dz;
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch)
+                        c[ch] = c[ch] - SH_C1 * Y * SHV(1, ch) + SH_C1 * Z * SHV(2, ch) - SH_C1 * X * SHV(3, ch);
+                    if (ncoef >= 9) {
+                        const float xx = X * X, yy = Y * Y, zz = Z * Z;
+                        const float xy = X * Y, yz = Y * Z, xz = X * Z;
+#pragma unroll
+                        for (int ch = 0; ch < 3; ++ch)
+                            c[ch] = c[ch] + SH_C2_0 * xy * SHV(4, ch) + SH_C2_1 * yz * SHV(5, ch) +
+                                    SH_C2_2 * (2.0f * zz - xx - yy) * SHV(6, ch) + SH_C2_3 * xz * SHV(7, ch) +
+                                    SH_C2_4 * (xx - yy) * SHV(8, ch);
+                        if (ncoef >= 16) {
+#pragma unroll
+                            for (int ch = 0; ch < 3; ++ch)
+                                c[ch] = c[ch] + SH_C3_0 * Y * (3.0f * xx - yy) * SHV(9, ch) + SH_C3_1 * xy * Z * SHV(10, ch) +
+                                        SH_C3_2 * Y * (4.0f * zz - xx - yy) * SHV(11, ch) +
+                                        SH_C3_3 * Z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SHV(12, ch) +
+                                        SH_C3_4 * X * (4.0f * zz - xx - yy) * SHV(13, ch) +
+                                        SH_C3_5 * Z * (xx - yy) * SHV(14, ch) + SH_C3_6 * X * (xx - 3.0f * yy) * SHV(15, ch);
+                        }
+                    }
+                }
+#undef SHV
+                c0 = c[0] + 0.5f; c1 = c[1] + 0.5f; c2 = c[2] + 0.5f;
+            }
+            if (DEBUG) {
+                vs[0] = 1.f; vs[1] = ndcx; vs[2] = ndcy; vs[3] = ndc2; vs[4] = hx; vs[5] = hy;
+                vs[6] = conic0; vs[7] = conic1; vs[8] = conic2; vs[9] = c0; vs[10] = c1; vs[11] = c2;
+                vs[12] = alpha; vs[13] = depth;
+            }
+            // ---- raster set-up (oracle/gs_oracle.c setup_one): depth clip, viewport, pixel rect
+            if (ndc2 >= -1.f && ndc2 <= 1.f) {
+                cx = ((ndcx + 1.f) * 0.5f) * (float)P.W;
+                cy = ((ndcy + 1.f) * 0.5f) * (float)P.H;
+                if (finitef(cx) && finitef(cy) && finitef(hx) && finitef(hy)) {
+                    imin = cover_lo(cx, hx, P.W); imax = cover_hi(cx, hx, P.W);
+                    jmin = cover_lo(cy, hy, P.H); jmax = cover_hi(cy, hy, P.H);
+                    ok = (imin <= imax && jmin <= jmax);
+                }
+            }
+        }
+        // ---- outputs
+        unsigned tiles = 0;
+        if (ok) {
+            const int tx0 = imin / GSR_TILE, tx1 = imax / GSR_TILE, ty0 = jmin / GSR_TILE, ty1 = jmax / GSR_TILE;
+            tiles = (unsigned)((tx1 - tx0 + 1) * (ty1 - ty0 + 1));
+            // source-colour clamp of a normalised target (ref_driver.inc); mode -4 scales the colour per
+            // fragment first, so only the lower clamp can be applied here
+            if (P.flags & 1u) {
+                if (mod == -4) { c0 = gl_max(c0, 0.f); c1 = gl_max(c1, 0.f); c2 = gl_max(c2, 0.f); }
+                else {
+                    c0 = gl_min(gl_max(c0, 0.f), 1.f); c1 = gl_min(gl_max(c1, 0.f), 1.f); c2 = gl_min(gl_max(c2, 0.f), 1.f);
+                }
+            }
+            const unsigned rx = (unsigned)imin | ((unsigned)(imax - imin) << 16);
+            const unsigned ry = (unsigned)jmin | ((unsigned)(jmax - jmin) << 16);
+            out.rec0[g] = make_float4(cx, cy, __uint_as_float(rx), __uint_as_float(ry));
+            out.rec1[g] = make_float4(conic0, conic1, conic2, alpha);
+            out.rec2[g] = make_float4(c0, c1, c2, depth);
+        }
+        out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
+        out.tiles[g] = tiles;
+        if (DEBUG) {
+            float4* d = reinterpret_cast<float4*>(out.dbg_vsout + 16 * (size_t)g);
+            d[0] = make_float4(vs[0], vs[1], vs[2], vs[3]);
+            d[1] = make_float4(vs[4], vs[5], vs[6], vs[7]);
+            d[2] = make_float4(vs[8], vs[9], vs[10], vs[11]);
+            d[3] = make_float4(vs[12], vs[13], 0.f, 0.f);
+            int4* e = reinterpret_cast<int4*>(out.dbg_setup + 8 * (size_t)g);
+            const bool clip_ok = !culled && (ndc2 >= -1.f && ndc2 <= 1.f);
+            e[0] = make_int4(__float_as_int(clip_ok ? cx : 0.f), __float_as_int(clip_ok ? cy : 0.f),
+                             __float_as_int(clip_ok ? depth : 0.f), ok ? 1 : 0);
+            e[1] = make_int4(imin, imax, jmin, jmax);
+        }
+    }
+    // visible count: one atomic per CTA
+    const unsigned b = __ballot_sync(0xffffffffu, ok);
+    if ((threadIdx.x & 31) == 0 && b) atomicAdd(&s_visible, __popc(b));
+    __syncthreads();
+    if (threadIdx.x == 0 && s_visible) atomicAdd(&counters->n_visible, s_visible);
+}
+
+__global__ void k_set_params(FrameParams* dst, FrameParams fp, FrameCounters* counters) {
+    if (threadIdx.x == 0) {
+        *dst = fp;
+        if (counters) { counters->n_visible = 0; counters->n_instances = 0; counters->overflow = 0; counters->pad = 0; }
+    }
+}
+
+__global__ void k_pack_scene(const float* __restrict__ rot, const float* __restrict__ scale,
+                             const float* __restrict__ opacity, float4* __restrict__ rot4,
+                             float4* __restrict__ scale_op, long long n) {
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    rot4[g] = make_float4(rot[4 * g + 0], rot[4 * g + 1], rot[4 * g + 2], rot[4 * g + 3]);
+    scale_op[g] = make_float4(scale[3 * g + 0], scale[3 * g + 1], scale[3 * g + 2], opacity[g]);
+}
+
+// keys for the global far->near order of sort_and_update: ascending view z, -0 == +0, NaN last
+// (/root/reference/renderer_ogl.py:10-19; oracle/gs_oracle.c f32_sort_key)
+struct View16 { float m[16]; };
+__global__ void k_depth_keys(const float* __restrict__ xyz, View16 vm, uint32_t* __restrict__ keys, long long n) {
+    const float* view = vm.m;
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n) return;
+    const float x = __ldg(xyz + 3 * g), y = __ldg(xyz + 3 * g + 1), z = __ldg(xyz + 3 * g + 2);
+    float d = ((view[8] * x + view[9] * y) + view[10] * z) + view[11];
+    uint32_t k;
+    if (d != d) k = 0xFFFFFFFFu;
+    else {
+        d = d + 0.0f;
+        const uint32_t u = __float_as_uint(d);
+        k = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+    }
+    keys[g] = k;
+}
+
+}  // namespace
+
+void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s) {
+    k_set_params<<<1, 32, 0, s>>>(dst, fp, counters);
+}
+
+void launch_pack_scene(const float* rot, const float* scale, const float* opacity, float4* rot4, float4* scale_op,
+                       long long n, cudaStream_t s) {
+    if (n <= 0) return;
+    k_pack_scene<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(rot, scale, opacity, rot4, scale_op, n);
+}
+
+void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
+                       long long n, int sh_dim, cudaStream_t s) {
+    if (n <= 0) return;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    const bool dbg = out.dbg_vsout != nullptr;
+    if (sh_dim == 48) {
+        if (dbg) k_preprocess<48, true><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        else k_preprocess<48, false><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+    } else {
+        if (dbg) k_preprocess<0, true><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        else k_preprocess<0, false><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+    }
+}
+
+void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s) {
+    if (n <= 0) return;
+    View16 vm;
+    for (int i = 0; i < 16; ++i) vm.m[i] = view16_host[i];
+    k_depth_keys<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(xyz, vm, keys, n);
+}

@@ -1,0 +1,313 @@
+// K3 — hand-written onesweep LSB radix sort (key/value pairs) for sm_100a.
+//
+// Replaces the torch / cupy / numpy argsort of /root/reference/renderer_ogl.py:10-53 and the CUB
+// DeviceRadixSort inside diff_gaussian_rasterization.  Stable, 8-bit digits, 32- or 64-bit keys,
+// 32-bit values.
+//
+//   k_rs_hist : ONE read of the keys builds the digit histograms of ALL passes (shared-memory
+//               histograms, one global atomic per bin per CTA) and clears the first look-back buffer.
+//   k_rs_pass : one kernel per digit.  Persistent CTAs take tiles in ticket order; each tile is ranked
+//               with warp match_any + per-warp digit counters, its per-digit counts are chained to
+//               the previous tiles with decoupled look-back (single 32-bit status word per
+//               (tile, digit): 2 flag bits + 30 count bits), and keys/values are scattered through
+//               shared memory so global stores are contiguous per digit run.  No global memory
+//               round trip between "count" and "scatter": keys are read once and written once per
+//               pass (the onesweep property).
+//
+// Item counts may live on the device (n_dev): grids are sized for the SM count, not for n, so the
+// same launch (and the same captured CUDA graph) serves any n up to the buffer capacity.
+#include "gsr_internal.h"
+
+namespace {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr uint32_t RS_FLAG_AGG = 1u << 30;
+constexpr uint32_t RS_FLAG_INC = 2u << 30;
+constexpr uint32_t RS_FLAG_MASK = 3u << 30;
+constexpr uint32_t RS_VAL_MASK = (1u << 30) - 1u;
+
+template <typename KeyT> struct RsCfg;
+template <> struct RsCfg<uint32_t> { static constexpr int ITEMS = 16; };
+template <> struct RsCfg<uint64_t> { static constexpr int ITEMS = 12; };
+
+struct RsPasses {
+    int n;
+    int shift[8];
+    int bits[8];
+};
+
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// exclusive scan of one value per thread over a 256-thread block; returns the exclusive prefix and the
+// block total via *total.  s_tmp: RS_WARPS + 1 words.
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* s_tmp, uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_tmp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = (lane < RS_WARPS) ? s_tmp[lane] : 0u;
+        uint32_t wi = w;
+#pragma unroll
+        for (int o = 1; o < RS_WARPS; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        if (lane < RS_WARPS) s_tmp[lane] = wi - w;
+        if (lane == RS_WARPS - 1) s_tmp[RS_WARPS] = wi;
+    }
+    __syncthreads();
+    const uint32_t res = s_tmp[warp] + incl - v;
+    if (total) *total = s_tmp[RS_WARPS];
+    __syncthreads();  // s_tmp may be reused by the caller
+    return res;
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const KeyT* __restrict__ keys, long long n_host,
+                                                       const uint32_t* __restrict__ n_dev, long long capacity,
+                                                       RsPasses passes, uint32_t* __restrict__ hist,
+                                                       uint32_t* __restrict__ status0) {
+    __shared__ uint32_t s_hist[8 * 256];
+    long long n = n_dev ? (long long)(*n_dev) : n_host;
+    if (n > capacity) n = capacity;
+    for (int i = threadIdx.x; i < passes.n * 256; i += RS_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    const long long stride = (long long)gridDim.x * RS_THREADS;
+    for (long long i = (long long)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+        const KeyT k = keys[i];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+            if (p < passes.n) {
+                const uint32_t d = (uint32_t)(k >> passes.shift[p]) & ((1u << passes.bits[p]) - 1u);
+                // warp-aggregated shared atomic: depth keys concentrate in a few high digits
+                const uint32_t peers = __match_any_sync(__activemask(), d);
+                if ((threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&s_hist[p * 256 + d], __popc(peers));
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes.n * 256; i += RS_THREADS) {
+        const uint32_t c = s_hist[i];
+        if (c) atomicAdd(&hist[i], c);
+    }
+    // clear the look-back rows the first pass will use
+    constexpr int TILE = RS_THREADS * RsCfg<KeyT>::ITEMS;
+    const long long rows = (n + TILE - 1) / TILE;
+    for (long long i = (long long)blockIdx.x * RS_THREADS + threadIdx.x; i < rows * 256; i += stride) status0[i] = 0;
+}
+
+template <typename KeyT, bool IDENTITY_VALS>
+__global__ void __launch_bounds__(RS_THREADS) k_rs_pass(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+                                                       const uint32_t* __restrict__ vals_in,
+                                                       uint32_t* __restrict__ vals_out, long long n_host,
+                                                       const uint32_t* __restrict__ n_dev, long long capacity,
+                                                       int shift, int bits, const uint32_t* __restrict__ hist,
+                                                       uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_cur,
+                                                       uint32_t* __restrict__ status_next) {
+    constexpr int ITEMS = RsCfg<KeyT>::ITEMS;
+    constexpr int TILE = RS_THREADS * ITEMS;
+    __shared__ KeyT s_keys[TILE];
+    __shared__ uint32_t s_vals[TILE];
+    __shared__ uint32_t s_whist[RS_WARPS][256];
+    __shared__ uint32_t s_digit_start[256];
+    __shared__ uint32_t s_bin_base[256];
+    __shared__ uint32_t s_global_excl[256];
+    __shared__ uint32_t s_tmp[RS_WARPS + 1];
+    __shared__ uint32_t s_tile;
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t mask = (1u << bits) - 1u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    long long n = n_dev ? (long long)(*n_dev) : n_host;
+    if (n > capacity) n = capacity;
+
+    s_global_excl[t] = block_excl_scan_256(hist[t], s_tmp, nullptr);
+
+    while (true) {
+        if (t == 0) s_tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const long long tile = s_tile;
+        const long long tile_base = tile * TILE;
+        if (tile_base >= n) break;
+        const int n_valid = (int)((n - tile_base < TILE) ? (n - tile_base) : TILE);
+        status_next[tile * 256 + t] = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) s_whist[w][t] = 0;
+        __syncthreads();
+
+        // ---- load (warp-striped: item i of lane l is element warp_base + i*32 + l)
+        KeyT key[ITEMS];
+        uint32_t val[ITEMS];
+        const long long warp_base = tile_base + (long long)warp * (32 * ITEMS);
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const long long idx = warp_base + i * 32 + lane;
+            const bool valid = idx < n;
+            key[i] = valid ? keys_in[idx] : (KeyT)~(KeyT)0;
+            if (IDENTITY_VALS) val[i] = (uint32_t)idx;
+            else val[i] = valid ? vals_in[idx] : 0u;
+        }
+        // ---- rank inside the warp, digit counters per warp
+        uint32_t rank[ITEMS];
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+            const uint32_t peers = __match_any_sync(0xffffffffu, d);
+            const int leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if (lane == leader) {
+                old = s_whist[warp][d];
+                s_whist[warp][d] = old + __popc(peers);
+            }
+            old = __shfl_sync(0xffffffffu, old, leader);
+            rank[i] = old + __popc(peers & lt_mask);
+            __syncwarp();
+        }
+        __syncthreads();
+        // ---- per digit (thread t owns digit t): exclusive scan over warps, tile count
+        uint32_t count = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; ++w) {
+            const uint32_t c = s_whist[w][t];
+            s_whist[w][t] = count;
+            count += c;
+        }
+        // padding keys (all ones) sit in digit `mask`, after every valid key of that digit
+        const uint32_t count_pub = count - (((uint32_t)t == mask) ? (uint32_t)(TILE - n_valid) : 0u);
+        st_volatile_u32(&status_cur[tile * 256 + t], ((tile == 0) ? RS_FLAG_INC : RS_FLAG_AGG) | count_pub);
+        const uint32_t dstart = block_excl_scan_256(count, s_tmp, nullptr);
+        s_digit_start[t] = dstart;
+        // ---- decoupled look-back over previous tiles for digit t
+        uint32_t prefix = 0;
+        if (tile > 0) {
+            for (long long p = tile - 1;; --p) {
+                uint32_t w;
+                do { w = ld_volatile_u32(&status_cur[p * 256 + t]); } while ((w & RS_FLAG_MASK) == 0u);
+                prefix += w & RS_VAL_MASK;
+                if (w & RS_FLAG_INC) break;
+            }
+            st_volatile_u32(&status_cur[tile * 256 + t], RS_FLAG_INC | (prefix + count_pub));
+        }
+        s_bin_base[t] = s_global_excl[t] + prefix - dstart;
+        __syncthreads();
+        // ---- scatter into shared memory in tile-sorted order
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & mask;
+            const uint32_t pos = s_digit_start[d] + s_whist[warp][d] + rank[i];
+            s_keys[pos] = key[i];
+            s_vals[pos] = val[i];
+        }
+        __syncthreads();
+        // ---- contiguous runs per digit go out to global memory
+        for (int s = t; s < n_valid; s += RS_THREADS) {
+            const KeyT k = s_keys[s];
+            const uint32_t d = (uint32_t)(k >> shift) & mask;
+            const uint32_t dst = s_bin_base[d] + (uint32_t)s;
+            keys_out[dst] = k;
+            vals_out[dst] = s_vals[s];
+        }
+        __syncthreads();
+    }
+}
+
+int g_num_sms = 0;
+int num_sms() {
+    if (g_num_sms == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+        if (g_num_sms <= 0) g_num_sms = 148;
+    }
+    return g_num_sms;
+}
+
+}  // namespace
+
+size_t sort_scratch_bytes(long long max_items, int key_bytes) {
+    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::ITEMS : RsCfg<uint32_t>::ITEMS;
+    const long long tiles = (max_items + RS_THREADS * items - 1) / (RS_THREADS * items) + 1;
+    return (size_t)(8 * 256 + 64) * 4 + 2 * (size_t)tiles * 256 * 4;
+}
+
+void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key_bytes) {
+    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::ITEMS : RsCfg<uint32_t>::ITEMS;
+    const long long tiles = (max_items + RS_THREADS * items - 1) / (RS_THREADS * items) + 1;
+    uint32_t* p = reinterpret_cast<uint32_t*>(base);
+    s->hist = p;
+    s->tickets = p + 8 * 256;
+    s->zero_bytes = (size_t)(8 * 256 + 64) * 4;
+    s->status[0] = p + 8 * 256 + 64;
+    s->status[1] = s->status[0] + (size_t)tiles * 256;
+    s->max_tiles = tiles;
+}
+
+template <typename KeyT>
+int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
+                     long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
+                     SortScratch* scratch, cudaStream_t stream, long long* launch_count) {
+    RsPasses passes;
+    passes.n = 0;
+    for (int b = begin_bit; b < end_bit && passes.n < 8; b += 8) {
+        passes.shift[passes.n] = b;
+        passes.bits[passes.n] = (end_bit - b < 8) ? (end_bit - b) : 8;
+        ++passes.n;
+    }
+    for (int p = passes.n; p < 8; ++p) { passes.shift[p] = 0; passes.bits[p] = 1; }
+    if (passes.n == 0) return 0;
+    const long long upper = n_dev ? capacity : n_host;
+    if (upper <= 0) return 0;
+    cudaMemsetAsync(scratch->hist, 0, scratch->zero_bytes, stream);
+    constexpr int TILE = RS_THREADS * RsCfg<KeyT>::ITEMS;
+    const long long tiles_upper = (upper + TILE - 1) / TILE;
+    const int sms = num_sms();
+    {
+        long long g = (upper + RS_THREADS * 8 - 1) / (RS_THREADS * 8);
+        if (g > sms * 8) g = sms * 8;
+        if (g < 1) g = 1;
+        k_rs_hist<KeyT><<<(unsigned)g, RS_THREADS, 0, stream>>>(keys_first, n_host, n_dev, capacity, passes, scratch->hist,
+                                                               scratch->status[0]);
+        if (launch_count) ++*launch_count;
+    }
+    long long grid = tiles_upper < (long long)sms * 4 ? tiles_upper : (long long)sms * 4;
+    if (grid < 1) grid = 1;
+    const KeyT* kin = keys_first; KeyT* kout = keys_tmp; KeyT* kother = keys;
+    uint32_t* vin = vals; uint32_t* vout = vals_tmp;
+    for (int p = 0; p < passes.n; ++p) {
+        uint32_t* st_cur = scratch->status[p & 1];
+        uint32_t* st_next = scratch->status[(p + 1) & 1];
+        if (p == 0 && vals_identity)
+            k_rs_pass<KeyT, true><<<(unsigned)grid, RS_THREADS, 0, stream>>>(kin, kout, nullptr, vout, n_host, n_dev, capacity,
+                                                                            passes.shift[p], passes.bits[p],
+                                                                            scratch->hist + p * 256, scratch->tickets + p,
+                                                                            st_cur, st_next);
+        else
+            k_rs_pass<KeyT, false><<<(unsigned)grid, RS_THREADS, 0, stream>>>(kin, kout, vin, vout, n_host, n_dev, capacity,
+                                                                             passes.shift[p], passes.bits[p],
+                                                                             scratch->hist + p * 256, scratch->tickets + p,
+                                                                             st_cur, st_next);
+        if (launch_count) ++*launch_count;
+        kin = kout; { KeyT* tk = kout; kout = kother; kother = tk; }
+        uint32_t* tv = vin; vin = vout; vout = tv;
+    }
+    return passes.n & 1;
+}
+
+template int radix_sort_pairs<uint32_t>(const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, bool, long long, const uint32_t*,
+                                        long long, int, int, SortScratch*, cudaStream_t, long long*);
+template int radix_sort_pairs<uint64_t>(const uint64_t*, uint64_t*, uint64_t*, uint32_t*, uint32_t*, bool, long long, const uint32_t*,
+                                        long long, int, int, SortScratch*, cudaStream_t, long long*);
