@@ -56,6 +56,8 @@ SIGNATURES = {
     "gsr_scene_buffer": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_ll)]),
     "gsr_alloc_gaussians": (C.c_int, [_vp, _ll, C.c_int]),
     "gsr_launch_count": (_ll, [_vp]),
+    "gsr_measure_peaks": (C.c_int, [_vp, _fp, _fp, _fp]),
+    "gsr_count_pairs": (C.c_int, [_vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
 }
 
 _lib = None

@@ -22,6 +22,7 @@ SOURCES = {
     "radix_sort.cu": [],
     "binning.cu": [],
     "blend.cu": [],
+    "instrument.cu": [],
     "gsr_api.cu": ["-Xcompiler", "-fvisibility=default"],
 }
 

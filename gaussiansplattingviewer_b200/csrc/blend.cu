@@ -15,10 +15,11 @@ namespace {
 constexpr int BL_THREADS = GSR_TILE * GSR_TILE;
 
 // MODE: 0 = gaussian falloff (render_mod >= 0 or -1), 2 = billboard (-2), 3 = flat ball (-3), 4 = gaussian ball (-4)
-template <int MODE>
+template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(BL_THREADS) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
                                                      const uint32_t* __restrict__ inst_gid, SplatBuffers sp,
-                                                     float* __restrict__ out_rgba, unsigned flags) {
+                                                     float* __restrict__ out_rgba, unsigned flags,
+                                                     unsigned long long* __restrict__ pair_counts) {
     __shared__ float4 s0[BL_THREADS];
     __shared__ float4 s1[BL_THREADS];
     __shared__ float4 s2[BL_THREADS];
@@ -33,6 +34,7 @@ __global__ void __launch_bounds__(BL_THREADS) k_blend(const FrameParams* __restr
     bool done = !inside;
     float T = 1.f, cr = 0.f, cg = 0.f, cb = 0.f;
     const bool clamp = (flags & 1u) != 0u;
+    unsigned n_eval = 0, n_hit = 0;  // COUNT only: (pixel, splat) pairs visited / pairs that contributed
 
     for (int start = range.x; start < range.y; start += BL_THREADS) {
         if (__syncthreads_count(done) == BL_THREADS) break;
@@ -48,12 +50,14 @@ __global__ void __launch_bounds__(BL_THREADS) k_blend(const FrameParams* __restr
         if (__all_sync(0xffffffffu, done)) continue;  // whole warp finished: skip the batch
         for (int j = 0; j < cnt && !done; ++j) {
             const float4 a = s0[j];
+            if (COUNT) ++n_eval;
             const uint32_t rx = __float_as_uint(a.z), ry = __float_as_uint(a.w);
             // pixel-rect test == |dx| <= hx && |dy| <= hy of the quad (exact, see preprocess.cu)
             if ((uint32_t)(px - (int)(rx & 0xFFFFu)) > (rx >> 16)) continue;
             if ((uint32_t)(py - (int)(ry & 0xFFFFu)) > (ry >> 16)) continue;
             const float4 c = s2[j];
             if (MODE == 2) {  // billboard: opaque quad
+                if (COUNT) ++n_hit;
                 cr += T * c.x; cg += T * c.y; cb += T * c.z;
                 T = 0.f; done = true;
                 break;
@@ -65,6 +69,7 @@ __global__ void __launch_bounds__(BL_THREADS) k_blend(const FrameParams* __restr
             const float e = __expf(power);
             const float alpha = fminf(0.99f, b.w * e);
             if (alpha < 1.f / 255.f) continue;
+            if (COUNT) ++n_hit;
             if (MODE == 0) {
                 const float w = alpha * T;
                 cr += w * c.x; cg += w * c.y; cb += w * c.z;
@@ -87,6 +92,17 @@ __global__ void __launch_bounds__(BL_THREADS) k_blend(const FrameParams* __restr
         float4* o = reinterpret_cast<float4*>(out_rgba) + (size_t)(H - 1 - py) * (size_t)W + px;
         *o = make_float4(cr, cg, cb, 1.f - T);
     }
+    if (COUNT) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            n_eval += __shfl_xor_sync(0xffffffffu, n_eval, o);
+            n_hit += __shfl_xor_sync(0xffffffffu, n_hit, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&pair_counts[0], (unsigned long long)n_eval);
+            atomicAdd(&pair_counts[1], (unsigned long long)n_hit);
+        }
+    }
 }
 
 __global__ void k_pack_rgb8(const float4* __restrict__ rgba, uint8_t* __restrict__ rgb, long long n_px) {
@@ -106,13 +122,27 @@ __global__ void k_extract_r(const float4* __restrict__ rgba, float* __restrict__
 
 }  // namespace
 
+template <bool COUNT>
+static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
+                           float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
+                           unsigned long long* pc, cudaStream_t s) {
+    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
+    if (render_mod == -2) k_blend<2, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+    else if (render_mod == -3) k_blend<3, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+    else if (render_mod == -4) k_blend<4, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+    else k_blend<0, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+}
+
 void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp, float* out_rgba,
                   int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s) {
-    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
-    if (render_mod == -2) k_blend<2><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags);
-    else if (render_mod == -3) k_blend<3><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags);
-    else if (render_mod == -4) k_blend<4><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags);
-    else k_blend<0><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags);
+    launch_blend_t<false>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, nullptr, s);
+}
+
+// Instrumented variant: same image, plus pair_counts[0] += pairs visited, [1] += pairs that contributed.
+void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
+                        float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
+                        unsigned long long* pair_counts, cudaStream_t s) {
+    launch_blend_t<true>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pair_counts, s);
 }
 
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s) {

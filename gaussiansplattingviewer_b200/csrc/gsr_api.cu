@@ -507,7 +507,9 @@ int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_i
 
 int gsr_sort_pairs(gsr_t* h, int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, long long n,
                    int begin_bit, int end_bit, void* stream) {
-    if (!h || !keys || !keys_tmp || !vals_tmp) return fail(GSR_EINVAL, "null argument");
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    if (n == 0) return 0;
+    if (!keys || !keys_tmp || !vals_tmp) return fail(GSR_EINVAL, "null argument");
     if (key_bits != 32 && key_bits != 64) return fail(GSR_EINVAL, "key_bits must be 32 or 64");
     if (begin_bit < 0 || end_bit > key_bits || begin_bit > end_bit) return fail(GSR_EINVAL, "bad bit range");
     if (n < 0 || n > MAX_CAPACITY) return fail(GSR_EINVAL, "bad n");
@@ -600,5 +602,31 @@ int gsr_debug_fetch(gsr_t* h, int which, void* dst, long long capacity_bytes, lo
 }
 
 long long gsr_launch_count(gsr_t* h) { return h ? h->launches : 0; }
+
+int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy_gbs) {
+    if (!h || !fp32_tflops || !ex2_tops || !copy_gbs) return fail(GSR_EINVAL, "null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    if (measure_peaks_impl(fp32_tflops, ex2_tops, copy_gbs) != 0) return fail(GSR_ECUDA, "peak micro-benchmark failed");
+    return 0;
+}
+
+int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed) {
+    if (!h || !visited || !contributed) return fail(GSR_EINVAL, "null argument");
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    if (!h->frame_valid) return fail(GSR_EINVAL, "no frame rendered since the last state change");
+    unsigned long long* d = nullptr;
+    CK(cudaMalloc(&d, 16));
+    CK(cudaMemset(d, 0, 16));
+    launch_blend_count(h->d_fp, h->d_ranges, h->d_ivals[h->last_result_buf], h->sp, h->d_frame, h->fp.render_mod,
+                       h->fp.flags, h->tiles_x, h->tiles_y, d, 0);
+    unsigned long long out[2] = {0, 0};
+    CK(cudaMemcpy(out, d, 16, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    *visited = out[0];
+    *contributed = out[1];
+    return 0;
+}
 
 }  // extern "C"

@@ -96,3 +96,7 @@ void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStrea
 void launch_extract_r(const float* rgba, float* r, long long n_px, cudaStream_t s);
 void launch_keys64_from_sorted(const uint32_t* tile_keys, const uint32_t* gid, const uint32_t* depth_key,
                                const FrameCounters* counters, long long capacity, uint64_t* out, cudaStream_t s);
+void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
+                        float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
+                        unsigned long long* pair_counts, cudaStream_t s);
+int measure_peaks_impl(float* fp32_tflops, float* ex2_tops, float* copy_gbs);

@@ -258,6 +258,18 @@ class B200Renderer(GaussianRenderBase):
     def launch_count(self) -> int:
         return int(self._lib.gsr_launch_count(self._h))
 
+    def measure_peaks(self):
+        """(fp32 TFLOP/s, 1e12 ex2/s, copy GB/s) from micro-benchmarks on this device."""
+        a, b, c = C.c_float(), C.c_float(), C.c_float()
+        _gsr.check(self._lib.gsr_measure_peaks(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def count_pairs(self):
+        """(visited, contributed) (pixel, splat) pairs of the last frame's blend."""
+        a, b = C.c_ulonglong(), C.c_ulonglong()
+        _gsr.check(self._lib.gsr_count_pairs(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def debug_fetch(self, which, dtype, cols=None):
         nbytes = C.c_longlong()
         _gsr.check(self._lib.gsr_debug_fetch(self._h, which, None, 0, C.byref(nbytes)))

@@ -136,6 +136,14 @@ int gsr_alloc_gaussians(gsr_t* h, long long n, int sh_dim);
 /* number of kernels launched by this handle since creation (bench.py's gpu_launches) */
 long long gsr_launch_count(gsr_t* h);
 
+/* ---- measurement (bench.py) ---------------------------------------------------------------------- */
+/* micro-benchmarks for the blend kernel's roofline denominators: FP32 FMA TFLOP/s, 1e12 ex2/s, and a
+ * device copy GB/s (read + write).  Synchronises. */
+int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy_gbs);
+/* re-blends the last frame with counters: (pixel, splat) pairs visited before the pixel terminated, and
+ * pairs that contributed a fragment.  Synchronises; the frame buffer passed to the last draw is untouched. */
+int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed);
+
 #ifdef __cplusplus
 }
 #endif
