@@ -1,0 +1,54 @@
+"""Multi-GPU plumbing for pose batches (the render_all.py / camera_data.csv workload).
+
+The path shards over camera views: every rank holds the whole scene and renders its own slice of the
+pose list.  The only collective is ONE broadcast of the scene arrays at load time; nothing is exchanged
+per frame.  Works with any torch.distributed backend (NCCL on GPUs, gloo in the CPU tests).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from .util_gau import GaussianData
+
+_FIELDS = ("xyz", "rot", "scale", "opacity", "sh")
+_COLS = {"xyz": 3, "rot": 4, "scale": 3, "opacity": 1}
+
+
+def shard_range(n_items: int, rank: int, world: int):
+    """Contiguous, balanced slice [lo, hi) of n_items for `rank` (sizes differ by at most one)."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_round_robin(n_items: int, rank: int, world: int):
+    """Interleaved assignment, for trajectories whose per-pose cost varies along the path."""
+    return list(range(rank, n_items, world))
+
+
+def broadcast_scene(gaus, device, src: int = 0):
+    """Replicates a scene from rank `src` to every rank.  `gaus` is a GaussianData on the source rank
+    (ignored elsewhere).  Returns the five arrays as torch tensors on `device`, in GaussianData order."""
+    import torch
+    import torch.distributed as dist
+
+    rank = dist.get_rank()
+    meta = torch.zeros(2, dtype=torch.int64, device=device)
+    if rank == src:
+        meta[0], meta[1] = len(gaus), gaus.sh_dim
+    dist.broadcast(meta, src=src)
+    n, sh_dim = int(meta[0]), int(meta[1])
+    out = []
+    for f in _FIELDS:
+        cols = _COLS.get(f, sh_dim)
+        if rank == src:
+            t = torch.from_numpy(np.ascontiguousarray(getattr(gaus, f), dtype=np.float32).reshape(n, cols)).to(device)
+        else:
+            t = torch.empty((n, cols), dtype=torch.float32, device=device)
+        dist.broadcast(t, src=src)
+        out.append(t)
+    return out
+
+
+def tensors_to_gaussians(ts) -> GaussianData:
+    return GaussianData(*[t.cpu().numpy() for t in ts])

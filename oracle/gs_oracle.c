@@ -24,6 +24,7 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
+#include "../include/gs_tilecull.h"
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -370,16 +371,23 @@ int gso_visible_order(const GsoSetup* setup, int n, int* out_order) {
  * pixel rect overlaps; key = (tile_id << 32) | bits(depth), value = Gaussian index; stable sort by key
  * (ties keep ascending index).  tile_id = ty * tiles_x + tx with GL rows (ty = 0 at the bottom).
  * Pass keys = NULL to get the count only.  ranges: 2 * tiles_x * tiles_y ints (start, end). */
-long long gso_tile_instances(const GsoSetup* setup, int n, int W, int H, int tile, uint64_t* keys, uint32_t* vals,
-                             long long capacity, int* ranges) {
+long long gso_tile_instances(const GsoSetup* setup, const GsoVsOut* vs, int cull, int n, int W, int H, int tile,
+                             uint64_t* keys, uint32_t* vals, long long capacity, int* ranges) {
     const int tiles_x = (W + tile - 1) / tile, tiles_y = (H + tile - 1) / tile;
     long long total = 0;
+    if (tile != GS_TILE) cull = 0;
     for (int g = 0; g < n; ++g) {
         if (!setup[g].ok) continue;
         const int tx0 = setup[g].imin / tile, tx1 = setup[g].imax / tile;
         const int ty0 = setup[g].jmin / tile, ty1 = setup[g].jmax / tile;
+        /* include/gs_tilecull.h: drop tiles in which no pixel can reach alpha >= 1/255 */
+        const int test = cull && vs && ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= GS_CULL_MAX_TILES);
+        const float thr = test ? gs_cull_threshold(vs[g].alpha) : 0.f;
         for (int ty = ty0; ty <= ty1; ++ty)
             for (int tx = tx0; tx <= tx1; ++tx) {
+                if (test && !gs_tile_keep(setup[g].cx, setup[g].cy, setup[g].imin, setup[g].imax, setup[g].jmin,
+                                          setup[g].jmax, tx, ty, vs[g].conic[0], vs[g].conic[1], vs[g].conic[2], thr))
+                    continue;
                 if (keys) {
                     if (total >= capacity) return -1;
                     keys[total] = ((uint64_t)(uint32_t)(ty * tiles_x + tx) << 32) | (uint64_t)f32_bits(setup[g].depth);

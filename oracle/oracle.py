@@ -144,17 +144,20 @@ def visible_order(setup):
     return out[:m].copy()
 
 
-def tile_instances(setup, W, H, tile=16):
-    """-> (keys u64 sorted, vals u32, ranges (tiles, 2) int32)"""
+def tile_instances(setup, W, H, tile=16, vs=None, cull=False):
+    """-> (keys u64 sorted, vals u32, ranges (tiles, 2) int32).  cull: apply the include/gs_tilecull.h rule
+    (needs the vertex-stage outputs `vs`)."""
     L = oracle_lib()
     n = len(setup)
-    total = L.gso_tile_instances(setup.ctypes.data_as(C.c_void_p), C.c_int(n), C.c_int(W), C.c_int(H), C.c_int(tile),
-                                 None, None, C.c_longlong(0), None)
+    vsp = vs.ctypes.data_as(C.c_void_p) if vs is not None else None
+    cl = C.c_int(1 if (cull and vs is not None) else 0)
+    total = L.gso_tile_instances(setup.ctypes.data_as(C.c_void_p), vsp, cl, C.c_int(n), C.c_int(W), C.c_int(H),
+                                 C.c_int(tile), None, None, C.c_longlong(0), None)
     keys = np.zeros(max(total, 1), dtype=np.uint64)
     vals = np.zeros(max(total, 1), dtype=np.uint32)
     tiles = ((W + tile - 1) // tile) * ((H + tile - 1) // tile)
     ranges = np.zeros((tiles, 2), dtype=np.int32)
-    got = L.gso_tile_instances(setup.ctypes.data_as(C.c_void_p), C.c_int(n), C.c_int(W), C.c_int(H), C.c_int(tile),
+    got = L.gso_tile_instances(setup.ctypes.data_as(C.c_void_p), vsp, cl, C.c_int(n), C.c_int(W), C.c_int(H), C.c_int(tile),
                                _p(keys, C.c_uint64), _p(vals, C.c_uint32), C.c_longlong(total), _p(ranges, C.c_int))
     assert got == total
     return keys[:total], vals[:total], ranges
