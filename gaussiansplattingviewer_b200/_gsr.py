@@ -18,6 +18,8 @@ GSR_DBG_INST_KEYS = 2
 GSR_DBG_INST_VALS = 3
 GSR_DBG_RANGES = 4
 
+GSR_TUNE_BLEND_PPT = 0
+
 
 class Stats(C.Structure):
     _fields_ = [
@@ -57,6 +59,7 @@ SIGNATURES = {
     "gsr_alloc_gaussians": (C.c_int, [_vp, _ll, C.c_int]),
     "gsr_launch_count": (_ll, [_vp]),
     "gsr_measure_peaks": (C.c_int, [_vp, _fp, _fp, _fp]),
+    "gsr_tune": (C.c_int, [_vp, C.c_int, C.c_int]),
     "gsr_count_pairs": (C.c_int, [_vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
 }
 

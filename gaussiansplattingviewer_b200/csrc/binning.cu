@@ -1,13 +1,14 @@
 // K2 duplicate-with-keys and K4 tile ranges for sm_100a.
 //
-// K2 turns the per-Gaussian tile rectangles into the tile-instance list.  One pass, load balanced:
+// K2 turns the per-Gaussian tile rectangles into the tile-instance list.  One pass:
 //   * each CTA takes a chunk of 1024 Gaussians (in the order given: depth-sorted for the two-level
 //     path, index order for the 64-bit-key path), block-scans their tile counts, chains the chunk total
 //     to the previous chunks with a decoupled look-back (64-bit status word: 2 flag bits + count), so the
 //     prefix sum never makes a round trip through global memory;
-//   * instances are then emitted by INSTANCE index, not by Gaussian: thread j of the CTA finds the owner
-//     of instance j by binary search in the chunk's shared-memory offsets, so a Gaussian covering
-//     thousands of tiles is written by the whole CTA with fully coalesced stores.
+//   * instances are emitted warp-cooperatively: a warp walks its 128 Gaussians, broadcasts one
+//     rectangle at a time with shuffles and its 32 lanes write that Gaussian's instances (tile index by
+//     a multiply-high with a per-Gaussian magic reciprocal, no division, no search), so stores are
+//     contiguous runs; rectangles above DUP_BIG tiles are deferred and written by the whole CTA.
 // Counterpart of the scan + duplicateWithKeys + identifyTileRanges steps of the tile rasteriser the
 // reference's CUDA backend calls (/root/reference/renderer_cuda.py:211-224); the OpenGL backend has no
 // tiles (its draw is one instanced quad per Gaussian, renderer_ogl.py:175-179).
@@ -16,8 +17,10 @@
 namespace {
 
 constexpr int DUP_THREADS = 256;
+constexpr int DUP_WARPS = DUP_THREADS / 32;
 constexpr int DUP_ITEMS = 4;
 constexpr int DUP_CHUNK = DUP_THREADS * DUP_ITEMS;
+constexpr uint32_t DUP_BIG = 2048;  // instances; larger rectangles are expanded by the whole CTA
 constexpr unsigned long long CH_FLAG_AGG = 1ull << 62;
 constexpr unsigned long long CH_FLAG_INC = 2ull << 62;
 constexpr unsigned long long CH_FLAG_MASK = 3ull << 62;
@@ -32,6 +35,14 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned 
     asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// k / w for k < 65536 by multiply-high with magic = ceil(2^32 / w) (exact for k, w < 2^16); w == 1 and
+// huge rectangles take the plain paths.
+__device__ __forceinline__ uint32_t magic_of(uint32_t w) { return (w > 1u) ? (0xFFFFFFFFu / w + 1u) : 0u; }
+__device__ __forceinline__ uint32_t div_magic(uint32_t k, uint32_t w, uint32_t magic, bool small) {
+    if (w == 1u) return k;
+    return small ? __umulhi(k, magic) : k / w;
+}
+
 // KEYS64 = false: gid comes from sorted_gid, output key is the 32-bit tile id.
 // KEYS64 = true : gid is the running index, output key is (tile << 32) | depth bits.
 template <bool KEYS64>
@@ -42,60 +53,76 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
                                                           uint32_t* __restrict__ ticket, void* __restrict__ out_keys,
                                                           uint32_t* __restrict__ out_gid, unsigned n,
                                                           unsigned long long capacity) {
-    __shared__ uint32_t s_off[DUP_CHUNK];  // chunk-local exclusive instance offsets
-    __shared__ uint32_t s_gid[DUP_CHUNK];
-    __shared__ uint32_t s_rx[DUP_CHUNK];   // tx0 | (tiles wide) << 16
-    __shared__ uint32_t s_ty0[DUP_CHUNK];
-    __shared__ uint32_t s_warp[DUP_THREADS / 32 + 1];
+    __shared__ uint32_t s_warp[DUP_WARPS + 1];
     __shared__ uint32_t s_chunk;
     __shared__ unsigned long long s_prefix;
+    __shared__ uint32_t s_nbig;
+    __shared__ uint32_t s_big[DUP_CHUNK][4];  // off, rx, ry, gid of deferred rectangles
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int tiles_x = fp->tiles_x;
+    const uint32_t tiles_x = (uint32_t)fp->tiles_x;
     const unsigned n_chunks = (n + DUP_CHUNK - 1) / DUP_CHUNK;
 
+    auto emit = [&](unsigned long long dst, uint32_t tile, uint32_t g) {
+        if (dst < capacity) {
+            if (KEYS64)
+                reinterpret_cast<unsigned long long*>(out_keys)[dst] =
+                    ((unsigned long long)tile << 32) | (unsigned long long)__ldg(sp.depth_key + g);
+            else
+                reinterpret_cast<uint32_t*>(out_keys)[dst] = tile;
+            out_gid[dst] = g;
+        }
+    };
+
     while (true) {
-        if (t == 0) s_chunk = atomicAdd(ticket, 1u);
+        if (t == 0) { s_chunk = atomicAdd(ticket, 1u); s_nbig = 0; }
         __syncthreads();
         const unsigned chunk = s_chunk;
         if (chunk >= n_chunks) break;
-        const unsigned base = chunk * DUP_CHUNK + t * DUP_ITEMS;
-        uint32_t gid[DUP_ITEMS], cnt[DUP_ITEMS];
+        // ---- load: lane-strided inside the warp's 128 slots, so the gid reads coalesce
+        const unsigned wbase = chunk * DUP_CHUNK + warp * (32 * DUP_ITEMS);
+        uint32_t gid[DUP_ITEMS], cnt[DUP_ITEMS], rx[DUP_ITEMS], ry[DUP_ITEMS];
 #pragma unroll
         for (int i = 0; i < DUP_ITEMS; ++i) {
-            const unsigned r = base + i;
-            gid[i] = 0; cnt[i] = 0;
+            const unsigned r = wbase + i * 32 + lane;
+            gid[i] = 0; rx[i] = 0; ry[i] = 0;
             if (r < n) {
                 gid[i] = KEYS64 ? r : __ldg(sorted_gid + r);
-                cnt[i] = __ldg(sp.tiles + gid[i]);
+                const uint2 tr = __ldg(sp.trect + gid[i]);
+                rx[i] = tr.x; ry[i] = tr.y;
             }
+            cnt[i] = (rx[i] >> 16) * (ry[i] >> 16);
         }
-        uint32_t tsum = 0;
+        // ---- scan in slot order (slot = i * 32 + lane): per-round warp scans, then rounds, then warps
+        uint32_t off[DUP_ITEMS];
+        uint32_t wsum = 0;
 #pragma unroll
-        for (int i = 0; i < DUP_ITEMS; ++i) tsum += cnt[i];
-        // block exclusive scan of tsum
-        uint32_t incl = tsum;
+        for (int i = 0; i < DUP_ITEMS; ++i) {
+            uint32_t incl = cnt[i];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            off[i] = wsum + incl - cnt[i];
+            wsum += __shfl_sync(0xffffffffu, incl, 31);
         }
-        if (lane == 31) s_warp[warp] = incl;
+        if (lane == 0) s_warp[warp] = wsum;
         __syncthreads();
         if (warp == 0) {
-            uint32_t w = (lane < DUP_THREADS / 32) ? s_warp[lane] : 0u;
+            const uint32_t w = (lane < DUP_WARPS) ? s_warp[lane] : 0u;
             uint32_t wi = w;
 #pragma unroll
-            for (int o = 1; o < DUP_THREADS / 32; o <<= 1) {
+            for (int o = 1; o < DUP_WARPS; o <<= 1) {
                 const uint32_t v = __shfl_up_sync(0xffffffffu, wi, o);
                 if (lane >= o) wi += v;
             }
-            if (lane < DUP_THREADS / 32) s_warp[lane] = wi - w;
-            if (lane == DUP_THREADS / 32 - 1) s_warp[DUP_THREADS / 32] = wi;
+            if (lane < DUP_WARPS) s_warp[lane] = wi - w;
+            if (lane == DUP_WARPS - 1) s_warp[DUP_WARPS] = wi;
         }
         __syncthreads();
-        uint32_t off = s_warp[warp] + incl - tsum;
-        const uint32_t chunk_total = s_warp[DUP_THREADS / 32];
-        // chain the chunk total (thread 0), while the others stage their entries
+        const uint32_t chunk_total = s_warp[DUP_WARPS];
+        const uint32_t wexcl = s_warp[warp];
+        // ---- chain the chunk total (thread 0)
         if (t == 0) {
             unsigned long long prefix = 0;
             if (chunk == 0) {
@@ -117,50 +144,51 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
                 counters->overflow = (total > capacity) ? 1u : 0u;
             }
         }
+        // per-Gaussian reciprocal (owner lane), defer the huge ones
+        uint32_t magic[DUP_ITEMS];
 #pragma unroll
         for (int i = 0; i < DUP_ITEMS; ++i) {
-            const int slot = t * DUP_ITEMS + i;
-            s_off[slot] = off;
-            off += cnt[i];
-            s_gid[slot] = gid[i];
-            uint32_t rx = 0, ty0 = 0;
-            if (cnt[i]) {
-                const float4 r0 = __ldg(sp.rec0 + gid[i]);
-                const uint32_t px = __float_as_uint(r0.z), py = __float_as_uint(r0.w);
-                const uint32_t imin = px & 0xFFFFu, imax = imin + (px >> 16);
-                const uint32_t jmin = py & 0xFFFFu;
-                const uint32_t tx0 = imin / GSR_TILE, tx1 = imax / GSR_TILE;
-                rx = tx0 | ((tx1 - tx0 + 1) << 16);
-                ty0 = jmin / GSR_TILE;
+            magic[i] = magic_of(rx[i] >> 16);
+            off[i] += wexcl;
+            if (cnt[i] > DUP_BIG) {
+                const uint32_t b = atomicAdd(&s_nbig, 1u);
+                s_big[b][0] = off[i]; s_big[b][1] = rx[i]; s_big[b][2] = ry[i]; s_big[b][3] = gid[i];
+                cnt[i] = 0;
             }
-            s_rx[slot] = rx;
-            s_ty0[slot] = ty0;
         }
         __syncthreads();
         const unsigned long long prefix = s_prefix;
-        // ---- emit by instance index
-        for (uint32_t j = t; j < chunk_total; j += DUP_THREADS) {
-            // largest slot with s_off[slot] <= j and a non-zero count (zero-count slots share the offset
-            // of their successor, so take the LAST slot whose offset <= j)
-            int lo = 0, hi = DUP_CHUNK - 1;
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (s_off[mid] <= j) lo = mid; else hi = mid - 1;
+        // ---- warp-cooperative emission
+#pragma unroll
+        for (int i = 0; i < DUP_ITEMS; ++i) {
+            uint32_t todo = __ballot_sync(0xffffffffu, cnt[i] != 0u);
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1u;
+                const uint32_t o = __shfl_sync(0xffffffffu, off[i], src);
+                const uint32_t x = __shfl_sync(0xffffffffu, rx[i], src);
+                const uint32_t y = __shfl_sync(0xffffffffu, ry[i], src);
+                const uint32_t g = __shfl_sync(0xffffffffu, gid[i], src);
+                const uint32_t m = __shfl_sync(0xffffffffu, magic[i], src);
+                const uint32_t w = x >> 16, c = w * (y >> 16);
+                const uint32_t tile0 = (y & 0xFFFFu) * tiles_x + (x & 0xFFFFu);
+                for (uint32_t k = lane; k < c; k += 32) {
+                    const uint32_t row = div_magic(k, w, m, true);  // c <= DUP_BIG < 65536
+                    emit(prefix + o + k, tile0 + row * tiles_x + (k - row * w), g);
+                }
             }
-            const uint32_t k = j - s_off[lo];
-            const uint32_t rx = s_rx[lo];
-            const uint32_t wdt = rx >> 16;
-            const uint32_t ty = s_ty0[lo] + k / wdt, tx = (rx & 0xFFFFu) + k % wdt;
-            const uint32_t tile = ty * (uint32_t)tiles_x + tx;
-            const unsigned long long dst = prefix + j;
-            if (dst < capacity) {
-                const uint32_t g = s_gid[lo];
-                if (KEYS64)
-                    reinterpret_cast<unsigned long long*>(out_keys)[dst] =
-                        ((unsigned long long)tile << 32) | (unsigned long long)__ldg(sp.depth_key + g);
-                else
-                    reinterpret_cast<uint32_t*>(out_keys)[dst] = tile;
-                out_gid[dst] = g;
+        }
+        // ---- deferred rectangles: whole CTA
+        const uint32_t nbig = s_nbig;
+        for (uint32_t b = 0; b < nbig; ++b) {
+            const uint32_t o = s_big[b][0], x = s_big[b][1], y = s_big[b][2], g = s_big[b][3];
+            const uint32_t w = x >> 16, c = w * (y >> 16);
+            const uint32_t tile0 = (y & 0xFFFFu) * tiles_x + (x & 0xFFFFu);
+            const uint32_t m = magic_of(w);
+            const bool small = c <= 65536u;
+            for (uint32_t k = t; k < c; k += DUP_THREADS) {
+                const uint32_t row = div_magic(k, w, m, small);
+                emit(prefix + o + k, tile0 + row * tiles_x + (k - row * w), g);
             }
         }
         __syncthreads();

@@ -1,96 +1,177 @@
 // K5 — per-16x16-tile front-to-back alpha blend for sm_100a.
 //
-// One CTA per tile, one thread per pixel.  The tile's instance list (nearest first) is staged through
-// shared memory in batches of 256 splat records; every thread evaluates the fragment rule of
-// /root/reference/shaders/gau_frag.glsl:13-39 for its pixel and composites front to back, which equals
-// the reference's back-to-front SRC_ALPHA / ONE_MINUS_SRC_ALPHA blend over a black clear
-// (renderer_ogl.py:128-130, main.py:821):   C = sum_i c_i a_i T_i,  T_i = prod_{j<i} (1 - a_j).
+// One CTA per tile.  A thread owns PPT vertically adjacent pixels of one column (PPT = 4: 64 threads,
+// a warp covers a compact 16x8 block), so the three shared-memory reads of a splat record and the
+// x-dependent half of the quadratic form are paid once per PPT pixels.  The tile's instance list
+// (nearest first) is streamed through shared memory in double-buffered batches with cp.async
+// (LDGSTS): while batch b is blended, batch b+1's records are already in flight and batch b+2's
+// Gaussian indices are being read.  The per-pixel body is branch-free (predicated), which keeps all 32
+// lanes busy: the fragment rule of /root/reference/shaders/gau_frag.glsl:13-39
+//     power = -0.5 (A dx^2 + C dy^2) - B dx dy ; discard if power > 0
+//     alpha = min(0.99, opacity * exp(power))  ; discard if alpha < 1/255
+// is evaluated as ex2 of a conic pre-scaled by -0.5*log2(e) / -log2(e) in the preprocess kernel, and
+// composited front to back, which equals the reference's back-to-front SRC_ALPHA / ONE_MINUS_SRC_ALPHA
+// blend over a black clear (renderer_ogl.py:128-130, main.py:821):
+//     C = sum_i c_i a_i T_i,  T_i = prod_{j<i} (1 - a_j).
 // A pixel stops once T < 1e-4 (its remaining contribution is below 1e-4 of any colour); a warp skips a
-// batch when all its pixels have stopped (ballot) and the CTA leaves when every pixel has.
+// batch when all its pixels have stopped and the CTA leaves when every pixel has.
+// The quad test |dx| <= hx && |dy| <= hy is the oracle's coverage rule verbatim (pixel centre minus
+// splat centre against the 3-sigma half extents, gau_vert.glsl:174-178).
 // Modes: >= 0 SH colour, -1 disparity, -2 billboard, -3 flat ball, -4 gaussian ball.
 #include "gsr_internal.h"
 
 namespace {
 
-constexpr int BL_THREADS = GSR_TILE * GSR_TILE;
+constexpr int BL_BATCH = 128;  // records per shared-memory batch
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // MODE: 0 = gaussian falloff (render_mod >= 0 or -1), 2 = billboard (-2), 3 = flat ball (-3), 4 = gaussian ball (-4)
-template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(BL_THREADS) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
+template <int MODE, int PPT, bool COUNT>
+__global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
                                                      const uint32_t* __restrict__ inst_gid, SplatBuffers sp,
                                                      float* __restrict__ out_rgba, unsigned flags,
                                                      unsigned long long* __restrict__ pair_counts) {
-    __shared__ float4 s0[BL_THREADS];
-    __shared__ float4 s1[BL_THREADS];
-    __shared__ float4 s2[BL_THREADS];
+    constexpr int THREADS = 256 / PPT;
+    constexpr int PER_THREAD = (BL_BATCH + THREADS - 1) / THREADS;  // records staged per thread per batch
+    __shared__ __align__(16) float4 s0[2][BL_BATCH];
+    __shared__ __align__(16) float4 s1[2][BL_BATCH];
+    __shared__ __align__(16) float4 s2[2][BL_BATCH];
     const int W = fp->W, H = fp->H;
     const int tile = blockIdx.y * gridDim.x + blockIdx.x;
-    const int lx = threadIdx.x & (GSR_TILE - 1), ly = threadIdx.x / GSR_TILE;
+    const int lx = threadIdx.x & (GSR_TILE - 1), lyb = threadIdx.x / GSR_TILE;
     const int px = blockIdx.x * GSR_TILE + lx;
-    const int py = blockIdx.y * GSR_TILE + ly;  // GL row, 0 = bottom
-    const bool inside = (px < W) && (py < H);
-    const float pxf = (float)px + 0.5f, pyf = (float)py + 0.5f;
+    const int py0 = blockIdx.y * GSR_TILE + lyb * PPT;  // GL row, 0 = bottom
+    const float pxf = (float)px + 0.5f;
+    float pyf[PPT], T[PPT], cr[PPT], cg[PPT], cb[PPT];
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+        pyf[k] = (float)(py0 + k) + 0.5f;
+        // pixels outside the image start terminated
+        T[k] = (px < W && py0 + k < H) ? 1.f : 0.f;
+        cr[k] = cg[k] = cb[k] = 0.f;
+    }
+    bool outside[PPT];
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) outside[k] = !(px < W && py0 + k < H);
     const int2 range = ranges[tile];
-    bool done = !inside;
-    float T = 1.f, cr = 0.f, cg = 0.f, cb = 0.f;
     const bool clamp = (flags & 1u) != 0u;
-    unsigned n_eval = 0, n_hit = 0;  // COUNT only: (pixel, splat) pairs visited / pairs that contributed
+    unsigned n_eval = 0, n_hit = 0;  // COUNT only
+    const int n_batches = (range.y - range.x + BL_BATCH - 1) / BL_BATCH;
 
-    for (int start = range.x; start < range.y; start += BL_THREADS) {
-        if (__syncthreads_count(done) == BL_THREADS) break;
-        const int idx = start + threadIdx.x;
-        if (idx < range.y) {
-            const uint32_t g = __ldg(inst_gid + idx);
-            s0[threadIdx.x] = __ldg(sp.rec0 + g);
-            s1[threadIdx.x] = __ldg(sp.rec1 + g);
-            s2[threadIdx.x] = __ldg(sp.rec2 + g);
+    // ---- staging helpers: thread t stages records t, t + THREADS, ... of a batch
+    uint32_t gid_next[PER_THREAD];  // Gaussian indices of the batch after the one in flight
+    auto load_gids = [&](int b) {
+#pragma unroll
+        for (int i = 0; i < PER_THREAD; ++i) {
+            const int slot = threadIdx.x + i * THREADS;
+            const int idx = range.x + b * BL_BATCH + slot;
+            gid_next[i] = (slot < BL_BATCH && idx < range.y) ? __ldg(inst_gid + idx) : 0xFFFFFFFFu;
+        }
+    };
+    auto issue_batch = [&](int buf) {
+#pragma unroll
+        for (int i = 0; i < PER_THREAD; ++i) {
+            const int slot = threadIdx.x + i * THREADS;
+            const uint32_t g = gid_next[i];
+            if (g != 0xFFFFFFFFu) {
+                cp_async16(&s0[buf][slot], sp.rec0 + g);
+                cp_async16(&s1[buf][slot], sp.rec1 + g);
+                cp_async16(&s2[buf][slot], sp.rec2 + g);
+            }
+        }
+        cp_async_commit();
+    };
+
+    if (n_batches > 0) {
+        load_gids(0);
+        issue_batch(0);
+        if (n_batches > 1) load_gids(1);
+    }
+    for (int b = 0; b < n_batches; ++b) {
+        const int buf = b & 1;
+        if (b + 1 < n_batches) {
+            issue_batch(buf ^ 1);
+            if (b + 2 < n_batches) load_gids(b + 2);
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
         }
         __syncthreads();
-        const int cnt = min(BL_THREADS, range.y - start);
-        if (__all_sync(0xffffffffu, done)) continue;  // whole warp finished: skip the batch
-        for (int j = 0; j < cnt && !done; ++j) {
-            const float4 a = s0[j];
-            if (COUNT) ++n_eval;
-            const uint32_t rx = __float_as_uint(a.z), ry = __float_as_uint(a.w);
-            // pixel-rect test == |dx| <= hx && |dy| <= hy of the quad (exact, see preprocess.cu)
-            if ((uint32_t)(px - (int)(rx & 0xFFFFu)) > (rx >> 16)) continue;
-            if ((uint32_t)(py - (int)(ry & 0xFFFFu)) > (ry >> 16)) continue;
-            const float4 c = s2[j];
-            if (MODE == 2) {  // billboard: opaque quad
-                if (COUNT) ++n_hit;
-                cr += T * c.x; cg += T * c.y; cb += T * c.z;
-                T = 0.f; done = true;
-                break;
-            }
-            const float4 b = s1[j];
-            const float dx = pxf - a.x, dy = pyf - a.y;
-            const float power = -0.5f * (b.x * dx * dx + b.z * dy * dy) - b.y * dx * dy;
-            if (power > 0.f) continue;
-            const float e = __expf(power);
-            const float alpha = fminf(0.99f, b.w * e);
-            if (alpha < 1.f / 255.f) continue;
-            if (COUNT) ++n_hit;
-            if (MODE == 0) {
-                const float w = alpha * T;
-                cr += w * c.x; cg += w * c.y; cb += w * c.z;
-                T = T * (1.f - alpha);
-                if (T < 1e-4f) done = true;
-            } else {
-                if (alpha > 0.22f) {  // flat / gaussian ball: alpha becomes 1
-                    float r = c.x, g2 = c.y, bl = c.z;
-                    if (MODE == 4) {
-                        r *= e; g2 *= e; bl *= e;
-                        if (clamp) { r = fminf(r, 1.f); g2 = fminf(g2, 1.f); bl = fminf(bl, 1.f); }
+        bool live = false;
+#pragma unroll
+        for (int k = 0; k < PPT; ++k) live = live || (T[k] >= 1e-4f);
+        if (__any_sync(0xffffffffu, live)) {
+            const int cnt = min(BL_BATCH, range.y - range.x - b * BL_BATCH);
+#pragma unroll 2
+            for (int j = 0; j < cnt; ++j) {
+                const float4 a = s0[buf][j];  // cx, cy, hx, hy
+                const float4 q = s1[buf][j];  // A', B', C' (pre-scaled conic), opacity
+                const float4 c = s2[buf][j];  // r, g, b, depth
+                const float dx = pxf - a.x;
+                const bool inx = fabsf(dx) <= a.z;
+                const float bdx = q.y * dx;
+                const float adx2 = q.x * dx * dx;
+#pragma unroll
+                for (int k = 0; k < PPT; ++k) {
+                    const float dy = pyf[k] - a.y;
+                    bool valid = inx && (fabsf(dy) <= a.w) && (T[k] >= 1e-4f);
+                    if (COUNT) n_eval += (T[k] >= 1e-4f) ? 1u : 0u;
+                    if (MODE == 2) {  // billboard: opaque quad
+                        if (COUNT) n_hit += valid ? 1u : 0u;
+                        const float w = valid ? T[k] : 0.f;
+                        cr[k] = fmaf(w, c.x, cr[k]); cg[k] = fmaf(w, c.y, cg[k]); cb[k] = fmaf(w, c.z, cb[k]);
+                        T[k] -= w;
+                    } else {
+                        const float p2 = fmaf(fmaf(q.z, dy, bdx), dy, adx2);  // log2(e) * power
+                        const float e = ex2_approx(p2);
+                        const float alpha = fminf(0.99f, q.w * e);
+                        valid = valid && !(p2 > 0.f) && !(alpha < 1.f / 255.f);
+                        if (MODE == 0) {
+                            if (COUNT) n_hit += valid ? 1u : 0u;
+                            const float w = valid ? alpha * T[k] : 0.f;
+                            cr[k] = fmaf(w, c.x, cr[k]); cg[k] = fmaf(w, c.y, cg[k]); cb[k] = fmaf(w, c.z, cb[k]);
+                            T[k] -= w;
+                        } else {  // flat / gaussian ball: alpha becomes 1 above 0.22, 0 below
+                            const bool opaque = valid && (alpha > 0.22f);
+                            if (COUNT) n_hit += valid ? 1u : 0u;
+                            float r = c.x, g2 = c.y, bl = c.z;
+                            if (MODE == 4) {
+                                r *= e; g2 *= e; bl *= e;
+                                if (clamp) { r = fminf(r, 1.f); g2 = fminf(g2, 1.f); bl = fminf(bl, 1.f); }
+                            }
+                            const float w = opaque ? T[k] : 0.f;
+                            cr[k] = fmaf(w, r, cr[k]); cg[k] = fmaf(w, g2, cg[k]); cb[k] = fmaf(w, bl, cb[k]);
+                            T[k] -= w;
+                        }
                     }
-                    cr += T * r; cg += T * g2; cb += T * bl;
-                    T = 0.f; done = true;
                 }
             }
         }
+        bool live2 = false;
+#pragma unroll
+        for (int k = 0; k < PPT; ++k) live2 = live2 || (T[k] >= 1e-4f);
+        // also the barrier that protects buffer `buf` from the cp.async of the next iteration
+        if (__syncthreads_or(live2 ? 1 : 0) == 0) break;
     }
-    if (inside) {
-        float4* o = reinterpret_cast<float4*>(out_rgba) + (size_t)(H - 1 - py) * (size_t)W + px;
-        *o = make_float4(cr, cg, cb, 1.f - T);
+    cp_async_wait<0>();
+#pragma unroll
+    for (int k = 0; k < PPT; ++k) {
+        if (!outside[k]) {
+            float4* o = reinterpret_cast<float4*>(out_rgba) + (size_t)(H - 1 - (py0 + k)) * (size_t)W + px;
+            *o = make_float4(cr[k], cg[k], cb[k], 1.f - T[k]);
+        }
     }
     if (COUNT) {
 #pragma unroll
@@ -120,17 +201,34 @@ __global__ void k_extract_r(const float4* __restrict__ rgba, float* __restrict__
     if (i < n_px) r[i] = rgba[i].x;
 }
 
+int g_blend_ppt = 4;  // pixels per thread (1, 2 or 4); gsr_tune(GSR_TUNE_BLEND_PPT, v)
+
 }  // namespace
+
+void set_blend_ppt(int v) { if (v == 1 || v == 2 || v == 4) g_blend_ppt = v; }
+
+template <int PPT, bool COUNT>
+static void launch_blend_p(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
+                           float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
+                           unsigned long long* pc, cudaStream_t s) {
+    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
+    constexpr int TH = 256 / PPT;
+    if (render_mod == -2) k_blend<2, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+    else if (render_mod == -3) k_blend<3, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+    else if (render_mod == -4) k_blend<4, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+    else k_blend<0, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+}
 
 template <bool COUNT>
 static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                            float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
                            unsigned long long* pc, cudaStream_t s) {
-    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
-    if (render_mod == -2) k_blend<2, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
-    else if (render_mod == -3) k_blend<3, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
-    else if (render_mod == -4) k_blend<4, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
-    else k_blend<0, COUNT><<<grid, BL_THREADS, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
+    if (g_blend_ppt == 1)
+        launch_blend_p<1, COUNT>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pc, s);
+    else if (g_blend_ppt == 2)
+        launch_blend_p<2, COUNT>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pc, s);
+    else
+        launch_blend_p<4, COUNT>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pc, s);
 }
 
 void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp, float* out_rgba,

@@ -95,7 +95,7 @@ namespace {
 
 int free_gaussian_buffers(gsr_t* h) {
     dfree(h->d_xyz); dfree(h->d_rot); dfree(h->d_scale_op); dfree(h->d_sh);
-    dfree(h->sp.rec0); dfree(h->sp.rec1); dfree(h->sp.rec2); dfree(h->sp.depth_key); dfree(h->sp.tiles);
+    dfree(h->sp.rec0); dfree(h->sp.rec1); dfree(h->sp.rec2); dfree(h->sp.depth_key); dfree(h->sp.trect);
     dfree(h->sp.dbg_vsout); dfree(h->sp.dbg_setup);
     dfree(h->d_dkey[0]); dfree(h->d_dkey[1]); dfree(h->d_gid[0]); dfree(h->d_gid[1]);
     dfree(h->d_sortn); dfree(h->d_chain);
@@ -121,7 +121,7 @@ int alloc_gaussian_buffers(gsr_t* h, long long n, int sh_dim) {
     CK(cudaMalloc(&h->sp.rec1, n1 * sizeof(float4)));
     CK(cudaMalloc(&h->sp.rec2, n1 * sizeof(float4)));
     CK(cudaMalloc(&h->sp.depth_key, n1 * 4));
-    CK(cudaMalloc(&h->sp.tiles, n1 * 4));
+    CK(cudaMalloc(&h->sp.trect, n1 * sizeof(uint2)));
     for (int i = 0; i < 2; ++i) {
         CK(cudaMalloc(&h->d_dkey[i], n1 * 4));
         CK(cudaMalloc(&h->d_gid[i], n1 * 4));
@@ -609,6 +609,17 @@ int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy
     CK(cudaDeviceSynchronize());
     if (measure_peaks_impl(fp32_tflops, ex2_tops, copy_gbs) != 0) return fail(GSR_ECUDA, "peak micro-benchmark failed");
     return 0;
+}
+
+int gsr_tune(gsr_t* h, int key, int value) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    switch (key) {
+        case GSR_TUNE_BLEND_PPT:
+            if (value != 1 && value != 2 && value != 4) return fail(GSR_EINVAL, "blend ppt must be 1, 2 or 4");
+            set_blend_ppt(value);
+            return 0;
+        default: return fail(GSR_EINVAL, "unknown tuning key");
+    }
 }
 
 int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed) {

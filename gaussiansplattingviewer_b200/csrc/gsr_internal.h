@@ -29,9 +29,10 @@ struct FrameCounters {
 };
 
 // Splat record, three float4 planes indexed by Gaussian:
-//   rec0 = (cx, cy, bits(imin | (imax-imin) << 16), bits(jmin | (jmax-jmin) << 16))
-//   rec1 = (conic A, conic B, conic C, opacity)
+//   rec0 = (cx, cy, hx, hy)            splat centre (window coordinates) and 3-sigma half extents
+//   rec1 = (A', B', C', opacity)       conic pre-scaled: log2(e) * power = A' dx^2 + B' dx dy + C' dy^2
 //   rec2 = (r, g, b, depth)
+// plus the tile rectangle trect = (tx0 | tiles_wide << 16, ty0 | tiles_high << 16), 0 x 0 when culled.
 struct SceneBuffers {
     const float* xyz;      // N x 3
     const float4* rot;     // N (w, x, y, z)
@@ -44,7 +45,7 @@ struct SplatBuffers {
     float4* rec1;
     float4* rec2;
     uint32_t* depth_key;  // bits(depth) or 0xFFFFFFFF when not ok
-    uint32_t* tiles;      // tiles touched (0 when not ok)
+    uint2* trect;         // tile rectangle (0 x 0 when not ok)
     float* dbg_vsout;     // N x 16 or nullptr
     int32_t* dbg_setup;   // N x 8 or nullptr
 };
@@ -99,4 +100,5 @@ void launch_keys64_from_sorted(const uint32_t* tile_keys, const uint32_t* gid, c
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                         float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
                         unsigned long long* pair_counts, cudaStream_t s);
+void set_blend_ppt(int v);
 int measure_peaks_impl(float* fp32_tflops, float* ex2_tops, float* copy_gbs);

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
 #pragma unroll
         for (int k = 0; k < 16; ++k) vs[k] = 0.f;
         int imin = 0, imax = -1, jmin = 0, jmax = -1;
-        float cx = 0.f, cy = 0.f, depth = 0.f;
+        float cx = 0.f, cy = 0.f, depth = 0.f, hx = 0.f, hy = 0.f;
         float conic0 = 0.f, conic1 = 0.f, conic2 = 0.f, alpha = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
 
         if (!culled) {
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
             const float det = (ca * cc - cb * cb);
             const float det_inv = 1.f / det;
             conic0 = cc * det_inv; conic1 = -cb * det_inv; conic2 = ca * det_inv;
-            const float hx = 3.f * sqrtf(ca), hy = 3.f * sqrtf(cc);
+            hx = 3.f * sqrtf(ca); hy = 3.f * sqrtf(cc);
             alpha = so.w;
             // ---- colour
             if (mod == -1) {  // :182-211 disparity
@@ -262,10 +262,11 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
             }
         }
         // ---- outputs
-        unsigned tiles = 0;
+        uint2 trect = make_uint2(0u, 0u);  // tx0 | tiles wide << 16, ty0 | tiles high << 16 (0 x 0 when not ok)
         if (ok) {
             const int tx0 = imin / GSR_TILE, tx1 = imax / GSR_TILE, ty0 = jmin / GSR_TILE, ty1 = jmax / GSR_TILE;
-            tiles = (unsigned)((tx1 - tx0 + 1) * (ty1 - ty0 + 1));
+            trect.x = (unsigned)tx0 | ((unsigned)(tx1 - tx0 + 1) << 16);
+            trect.y = (unsigned)ty0 | ((unsigned)(ty1 - ty0 + 1) << 16);
             // source-colour clamp of a normalised target (ref_driver.inc); mode -4 scales the colour per
             // fragment first, so only the lower clamp can be applied here
             if (P.flags & 1u) {
@@ -274,14 +275,16 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
                     c0 = gl_min(gl_max(c0, 0.f), 1.f); c1 = gl_min(gl_max(c1, 0.f), 1.f); c2 = gl_min(gl_max(c2, 0.f), 1.f);
                 }
             }
-            const unsigned rx = (unsigned)imin | ((unsigned)(imax - imin) << 16);
-            const unsigned ry = (unsigned)jmin | ((unsigned)(jmax - jmin) << 16);
-            out.rec0[g] = make_float4(cx, cy, __uint_as_float(rx), __uint_as_float(ry));
-            out.rec1[g] = make_float4(conic0, conic1, conic2, alpha);
+            // blend-ready record: centre + half extents (the quad test |dx| <= hx, |dy| <= hy is evaluated per
+            // pixel exactly as the oracle does), conic pre-scaled so that the blend kernel gets
+            // log2(e) * power = A' dx^2 + B' dx dy + C' dy^2 with one ex2
+            const float L2E = 1.4426950408889634f;
+            out.rec0[g] = make_float4(cx, cy, hx, hy);
+            out.rec1[g] = make_float4(conic0 * (-0.5f * L2E), conic1 * (-L2E), conic2 * (-0.5f * L2E), alpha);
             out.rec2[g] = make_float4(c0, c1, c2, depth);
         }
         out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
-        out.tiles[g] = tiles;
+        out.trect[g] = trect;
         if (DEBUG) {
             float4* d = reinterpret_cast<float4*>(out.dbg_vsout + 16 * (size_t)g);
             d[0] = make_float4(vs[0], vs[1], vs[2], vs[3]);

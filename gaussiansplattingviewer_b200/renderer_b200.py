@@ -264,6 +264,10 @@ class B200Renderer(GaussianRenderBase):
         _gsr.check(self._lib.gsr_measure_peaks(self._h, C.byref(a), C.byref(b), C.byref(c)))
         return a.value, b.value, c.value
 
+    def tune(self, key: int, value: int):
+        """Kernel-variant knob for measurement runs (gsr_tune)."""
+        _gsr.check(self._lib.gsr_tune(self._h, int(key), int(value)))
+
     def count_pairs(self):
         """(visited, contributed) (pixel, splat) pairs of the last frame's blend."""
         a, b = C.c_ulonglong(), C.c_ulonglong()

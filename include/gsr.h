@@ -144,6 +144,11 @@ int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy
  * pairs that contributed a fragment.  Synchronises; the frame buffer passed to the last draw is untouched. */
 int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed);
 
+/* Kernel-variant knobs for measurement runs (process-wide; results are identical for every setting).
+ * GSR_TUNE_BLEND_PPT: pixels per thread of the blend kernel, 1, 2 or 4. */
+#define GSR_TUNE_BLEND_PPT 0
+int gsr_tune(gsr_t* h, int key, int value);
+
 #ifdef __cplusplus
 }
 #endif
