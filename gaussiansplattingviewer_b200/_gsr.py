@@ -19,6 +19,9 @@ GSR_DBG_INST_VALS = 3
 GSR_DBG_RANGES = 4
 
 GSR_TUNE_BLEND_PPT = 0
+GSR_TUNE_SORT_SMALL_TILES = 1
+GSR_TUNE_BLEND_SHAPE8 = 2
+GSR_TUNE_BLEND_SKIP = 3
 
 
 class Stats(C.Structure):

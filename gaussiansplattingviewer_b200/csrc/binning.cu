@@ -137,12 +137,7 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
                 }
                 st_volatile_u64(&chain[chunk], CH_FLAG_INC | (prefix + chunk_total));
             }
-            s_prefix = prefix;
-            if (chunk == n_chunks - 1) {
-                const unsigned long long total = prefix + chunk_total;
-                counters->n_instances = (total > 0xFFFFFFFFull) ? 0xFFFFFFFFu : (unsigned)total;
-                counters->overflow = (total > capacity) ? 1u : 0u;
-            }
+            s_prefix = prefix;  // D and the overflow flag come from k_tile_scan
         }
         // per-Gaussian reciprocal (owner lane), defer the huge ones
         uint32_t magic[DUP_ITEMS];
@@ -195,6 +190,114 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
     }
 }
 
+// K4' — tile counts, list offsets and sort histograms from the corner-impulse grid (one CTA).
+// The preprocess kernel added +1/-1/-1/+1 at the four corners of every visible Gaussian's tile rectangle;
+// the 2D inclusive prefix sum of that grid is the number of instances per tile.  From the counts follow
+//   ranges[tile] = [start, start + count)   (exclusive scan in tile-id order = order of the sorted list),
+//   the digit histograms of the two radix passes of the tile sort (no pass over the D instances needed),
+//   D itself and the overflow flag.
+constexpr int TS_THREADS = 1024;
+__global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid, int grid_stride, int gw, int TX, int TY, int bits0,
+                                                         int use_smem, unsigned long long capacity,
+                                                         int2* __restrict__ ranges, uint32_t* __restrict__ hist,
+                                                         FrameCounters* __restrict__ counters) {
+    extern __shared__ int s_dyn[];
+    __shared__ uint32_t s_hist[512];
+    __shared__ uint32_t s_wsum[TS_THREADS / 32 + 1];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int T = TX * TY;
+    int* w = use_smem ? s_dyn : grid;
+    for (int i = t; i < TY * gw; i += TS_THREADS) {  // sum the replicas
+        int v = 0;
+#pragma unroll
+        for (int r = 0; r < GSR_GRID_REPLICAS; ++r) v += grid[(size_t)r * grid_stride + i];
+        w[i] = v;
+    }
+    if (t < 512) s_hist[t] = 0;
+    __syncthreads();
+    // inclusive prefix along x: one warp per row, 32 columns per step
+    for (int r = warp; r < TY; r += TS_THREADS / 32) {
+        int carry = 0;
+        for (int c0 = 0; c0 < TX; c0 += 32) {
+            const int x = c0 + lane;
+            int v = (x < TX) ? w[r * gw + x] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += u;
+            }
+            v += carry;
+            if (x < TX) w[r * gw + x] = v;
+            carry = __shfl_sync(0xffffffffu, v, 31);
+        }
+    }
+    __syncthreads();
+    // inclusive prefix along y: one thread per column
+    for (int x = t; x < TX; x += TS_THREADS) {
+        int run = 0;
+        for (int y = 0; y < TY; ++y) { run += w[y * gw + x]; w[y * gw + x] = run; }
+    }
+    __syncthreads();
+    // exclusive scan of the counts in tile-id order; thread t owns ids [t * per, (t + 1) * per)
+    const int per = (T + TS_THREADS - 1) / TS_THREADS;
+    const int id0 = min(t * per, T), id1 = min(id0 + per, T);
+    unsigned long long sum = 0;
+    {
+        int y = id0 / TX, x = id0 - y * TX;
+        for (int id = id0; id < id1; ++id) {
+            sum += (unsigned)w[y * gw + x];
+            if (++x == TX) { x = 0; ++y; }
+        }
+    }
+    // block exclusive scan (64-bit: D may exceed 2^32 before the overflow check)
+    unsigned long long incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
+    }
+    __shared__ unsigned long long s_w64[TS_THREADS / 32 + 1];
+    if (lane == 31) s_w64[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        const unsigned long long v = s_w64[lane];
+        unsigned long long vi = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long u = __shfl_up_sync(0xffffffffu, vi, o);
+            if (lane >= o) vi += u;
+        }
+        s_w64[lane] = vi - v;
+        if (lane == 31) s_w64[32] = vi;
+    }
+    __syncthreads();
+    const unsigned long long total = s_w64[32];
+    const bool overflow = total > capacity;
+    unsigned long long start = s_w64[warp] + incl - sum;
+    {
+        const uint32_t mask0 = (1u << bits0) - 1u;
+        int y = id0 / TX, x = id0 - y * TX;
+        for (int id = id0; id < id1; ++id) {
+            const unsigned c = (unsigned)w[y * gw + x];
+            ranges[id] = (overflow || c == 0) ? make_int2(0, 0) : make_int2((int)start, (int)(start + c));  // empty: (0, 0)
+            if (c) {
+                atomicAdd(&s_hist[(uint32_t)id & mask0], c);
+                atomicAdd(&s_hist[256 + ((uint32_t)id >> bits0)], c);
+            }
+            start += c;
+            if (++x == TX) { x = 0; ++y; }
+        }
+    }
+    __syncthreads();
+    if (t < 512) hist[t] = s_hist[t];
+    if (t == 0) {
+        counters->n_instances = (total > 0xFFFFFFFFull) ? 0xFFFFFFFFu : (unsigned)total;
+        counters->overflow = overflow ? 1u : 0u;
+        counters->n_sort = overflow ? 0u : (unsigned)total;
+    }
+    (void)s_wsum;
+}
+
 template <typename KeyT>
 __global__ void __launch_bounds__(256) k_tile_ranges(const KeyT* __restrict__ keys, int key_shift,
                                                     const FrameCounters* __restrict__ counters, long long capacity,
@@ -213,14 +316,14 @@ __global__ void __launch_bounds__(256) k_tile_ranges(const KeyT* __restrict__ ke
     }
 }
 
-__global__ void k_keys64_from_sorted(const uint32_t* __restrict__ tile_keys, const uint32_t* __restrict__ gid,
-                                     const uint32_t* __restrict__ depth_key, const FrameCounters* __restrict__ counters,
-                                     long long capacity, unsigned long long* __restrict__ out) {
-    long long n = counters->n_instances;
-    if (n > capacity) n = capacity;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
-        out[i] = ((unsigned long long)tile_keys[i] << 32) | (unsigned long long)depth_key[gid[i]];
+// debug view of the sorted list as 64-bit keys: the two-level path never materialises them
+__global__ void k_keys64_from_ranges(const int2* __restrict__ ranges, int n_tiles, const uint32_t* __restrict__ gid,
+                                     const uint32_t* __restrict__ depth_key, unsigned long long* __restrict__ out) {
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int2 r = ranges[tile];
+        for (int i = r.x + threadIdx.x; i < r.y; i += blockDim.x)
+            out[i] = ((unsigned long long)(unsigned)tile << 32) | (unsigned long long)depth_key[gid[i]];
+    }
 }
 
 int sm_count() {
@@ -269,8 +372,26 @@ void launch_tile_ranges(const KeyT* sorted_keys, int key_shift, const FrameCount
 template void launch_tile_ranges<uint32_t>(const uint32_t*, int, const FrameCounters*, long long, int2*, int, cudaStream_t);
 template void launch_tile_ranges<uint64_t>(const uint64_t*, int, const FrameCounters*, long long, int2*, int, cudaStream_t);
 
-void launch_keys64_from_sorted(const uint32_t* tile_keys, const uint32_t* gid, const uint32_t* depth_key,
-                               const FrameCounters* counters, long long capacity, uint64_t* out, cudaStream_t s) {
-    k_keys64_from_sorted<<<sm_count() * 8, 256, 0, s>>>(tile_keys, gid, depth_key, counters, capacity,
+void launch_keys64_from_ranges(const int2* ranges, int n_tiles, const uint32_t* gid, const uint32_t* depth_key,
+                               uint64_t* out, cudaStream_t s) {
+    k_keys64_from_ranges<<<sm_count() * 8, 256, 0, s>>>(ranges, n_tiles, gid, depth_key,
                                                         reinterpret_cast<unsigned long long*>(out));
+}
+
+// Returns the dynamic shared memory the scan wants (0 = works in place in global memory).
+static size_t tile_scan_smem(int gw, int TY) {
+    const size_t need = (size_t)gw * TY * sizeof(int);
+    return need <= 200 * 1024 ? need : 0;
+}
+
+void launch_tile_scan(int* grid, int grid_stride, int gw, int tiles_x, int tiles_y, int bits0, long long capacity, int2* ranges,
+                      uint32_t* hist, FrameCounters* counters, cudaStream_t s) {
+    const size_t smem = tile_scan_smem(gw, tiles_y);
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        cudaFuncSetAttribute(k_tile_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024));
+        configured = 200 * 1024;
+    }
+    k_tile_scan<<<1, TS_THREADS, smem, s>>>(grid, grid_stride, gw, tiles_x, tiles_y, bits0, smem ? 1 : 0,
+                                             (unsigned long long)capacity, ranges, hist, counters);
 }

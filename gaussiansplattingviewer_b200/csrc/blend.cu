@@ -38,7 +38,7 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // MODE: 0 = gaussian falloff (render_mod >= 0 or -1), 2 = billboard (-2), 3 = flat ball (-3), 4 = gaussian ball (-4)
-template <int MODE, int PPT, bool COUNT>
+template <int MODE, int PPT, bool COUNT, bool SHAPE8, bool SKIP>
 __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
                                                      const uint32_t* __restrict__ inst_gid, SplatBuffers sp,
                                                      float* __restrict__ out_rgba, unsigned flags,
@@ -50,7 +50,18 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
     __shared__ __align__(16) float4 s2[2][BL_BATCH];
     const int W = fp->W, H = fp->H;
     const int tile = blockIdx.y * gridDim.x + blockIdx.x;
-    const int lx = threadIdx.x & (GSR_TILE - 1), lyb = threadIdx.x / GSR_TILE;
+    // pixel block of a warp: SHAPE8 = 8 columns x (4 * PPT) rows (compact: better quad / termination
+    // coherence), else 16 columns x (2 * PPT) rows
+    int lx, lyb;
+    if (SHAPE8) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        constexpr int WARPS_Y = GSR_TILE / (4 * PPT);  // warps stacked vertically per 8-column half
+        lx = (warp / WARPS_Y) * 8 + (lane & 7);
+        lyb = (warp % WARPS_Y) * 4 + (lane >> 3);
+    } else {
+        lx = threadIdx.x & (GSR_TILE - 1);
+        lyb = threadIdx.x / GSR_TILE;
+    }
     const int px = blockIdx.x * GSR_TILE + lx;
     const int py0 = blockIdx.y * GSR_TILE + lyb * PPT;  // GL row, 0 = bottom
     const float pxf = (float)px + 0.5f;
@@ -117,24 +128,34 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
 #pragma unroll 2
             for (int j = 0; j < cnt; ++j) {
                 const float4 a = s0[buf][j];  // cx, cy, hx, hy
-                const float4 q = s1[buf][j];  // A', B', C' (pre-scaled conic), opacity
-                const float4 c = s2[buf][j];  // r, g, b, depth
                 const float dx = pxf - a.x;
                 const bool inx = fabsf(dx) <= a.z;
+                float dy[PPT];
+                bool in[PPT];
+                bool any_in = false;
+#pragma unroll
+                for (int k = 0; k < PPT; ++k) {
+                    dy[k] = pyf[k] - a.y;
+                    if (COUNT) n_eval += (T[k] >= 1e-4f) ? 1u : 0u;
+                    in[k] = inx && (fabsf(dy[k]) <= a.w) && (T[k] >= 1e-4f);
+                    any_in = any_in || in[k];
+                }
+                // no live pixel of this warp lies inside the quad: skip the splat for 3 instructions
+                if (SKIP && !__any_sync(0xffffffffu, any_in)) continue;
+                const float4 q = s1[buf][j];  // A', B', C' (pre-scaled conic), opacity
+                const float4 c = s2[buf][j];  // r, g, b, depth
                 const float bdx = q.y * dx;
                 const float adx2 = q.x * dx * dx;
 #pragma unroll
                 for (int k = 0; k < PPT; ++k) {
-                    const float dy = pyf[k] - a.y;
-                    bool valid = inx && (fabsf(dy) <= a.w) && (T[k] >= 1e-4f);
-                    if (COUNT) n_eval += (T[k] >= 1e-4f) ? 1u : 0u;
+                    bool valid = in[k];
                     if (MODE == 2) {  // billboard: opaque quad
                         if (COUNT) n_hit += valid ? 1u : 0u;
                         const float w = valid ? T[k] : 0.f;
                         cr[k] = fmaf(w, c.x, cr[k]); cg[k] = fmaf(w, c.y, cg[k]); cb[k] = fmaf(w, c.z, cb[k]);
                         T[k] -= w;
                     } else {
-                        const float p2 = fmaf(fmaf(q.z, dy, bdx), dy, adx2);  // log2(e) * power
+                        const float p2 = fmaf(fmaf(q.z, dy[k], bdx), dy[k], adx2);  // log2(e) * power
                         const float e = ex2_approx(p2);
                         const float alpha = fminf(0.99f, q.w * e);
                         valid = valid && !(p2 > 0.f) && !(alpha < 1.f / 255.f);
@@ -201,34 +222,47 @@ __global__ void k_extract_r(const float4* __restrict__ rgba, float* __restrict__
     if (i < n_px) r[i] = rgba[i].x;
 }
 
-int g_blend_ppt = 4;  // pixels per thread (1, 2 or 4); gsr_tune(GSR_TUNE_BLEND_PPT, v)
+// kernel-variant knobs (gsr_tune): pixels per thread, warp block shape, warp-level quad skip
+int g_blend_ppt = 2, g_blend_shape8 = 1, g_blend_skip = 1;
 
 }  // namespace
 
 void set_blend_ppt(int v) { if (v == 1 || v == 2 || v == 4) g_blend_ppt = v; }
+void set_blend_shape8(int v) { g_blend_shape8 = v ? 1 : 0; }
+void set_blend_skip(int v) { g_blend_skip = v ? 1 : 0; }
 
-template <int PPT, bool COUNT>
-static void launch_blend_p(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
-                           float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
-                           unsigned long long* pc, cudaStream_t s) {
-    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
-    constexpr int TH = 256 / PPT;
-    if (render_mod == -2) k_blend<2, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
-    else if (render_mod == -3) k_blend<3, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
-    else if (render_mod == -4) k_blend<4, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
-    else k_blend<0, PPT, COUNT><<<grid, TH, 0, s>>>(fp, ranges, inst_gid, sp, out_rgba, flags, pc);
-}
+// default configuration (every mode, and the counting variant)
+constexpr int BL_PPT = 2;
+constexpr bool BL_SHAPE8 = true, BL_SKIP = true;
 
 template <bool COUNT>
 static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                            float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
                            unsigned long long* pc, cudaStream_t s) {
-    if (g_blend_ppt == 1)
-        launch_blend_p<1, COUNT>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pc, s);
-    else if (g_blend_ppt == 2)
-        launch_blend_p<2, COUNT>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pc, s);
-    else
-        launch_blend_p<4, COUNT>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pc, s);
+    const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
+    constexpr int TH = 256 / BL_PPT;
+#define BL_ARGS fp, ranges, inst_gid, sp, out_rgba, flags, pc
+    if (render_mod == -2) k_blend<2, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (render_mod == -3) k_blend<3, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (render_mod == -4) k_blend<4, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (COUNT) k_blend<0, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
+    else {
+        // measurement variants of the main mode
+        const int v = (g_blend_ppt == 4 ? 4 : (g_blend_ppt == 1 ? 8 : 0)) | (g_blend_shape8 ? 2 : 0) | (g_blend_skip ? 1 : 0);
+        switch (v) {
+            case 0: k_blend<0, 2, false, false, false><<<grid, 128, 0, s>>>(BL_ARGS); break;
+            case 1: k_blend<0, 2, false, false, true><<<grid, 128, 0, s>>>(BL_ARGS); break;
+            case 2: k_blend<0, 2, false, true, false><<<grid, 128, 0, s>>>(BL_ARGS); break;
+            case 3: k_blend<0, 2, false, true, true><<<grid, 128, 0, s>>>(BL_ARGS); break;
+            case 4: k_blend<0, 4, false, false, false><<<grid, 64, 0, s>>>(BL_ARGS); break;
+            case 5: k_blend<0, 4, false, false, true><<<grid, 64, 0, s>>>(BL_ARGS); break;
+            case 6: k_blend<0, 4, false, true, false><<<grid, 64, 0, s>>>(BL_ARGS); break;
+            case 7: k_blend<0, 4, false, true, true><<<grid, 64, 0, s>>>(BL_ARGS); break;
+            case 8: case 10: k_blend<0, 1, false, true, false><<<grid, 256, 0, s>>>(BL_ARGS); break;
+            default: k_blend<0, 1, false, true, true><<<grid, 256, 0, s>>>(BL_ARGS); break;
+        }
+    }
+#undef BL_ARGS
 }
 
 void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp, float* out_rgba,

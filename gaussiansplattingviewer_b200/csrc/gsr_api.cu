@@ -69,6 +69,8 @@ struct gsr_renderer {
     // image-side
     int W = 0, H = 0, tiles_x = 0, tiles_y = 0;
     int2* d_ranges = nullptr;
+    int* d_tile_grid = nullptr;  // (tiles_y + 1) x grid_w corner impulses
+    int grid_w = 0;
     float* d_frame = nullptr;
     uint8_t* d_rgb8 = nullptr;
     float* d_r32 = nullptr;
@@ -193,15 +195,25 @@ int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bo
     const int n_tiles = h->tiles_x * h->tiles_y;
     const int tbits = tile_bits(n_tiles);
     SceneBuffers scene = {h->d_xyz, h->d_rot, h->d_scale_op, h->d_sh};
-    const uint32_t* n_inst = &h->d_counters->n_instances;
+
+    // split of the tile-id bits between the two radix passes of the tile sort (k_tile_scan builds both
+    // digit histograms from the per-tile counts); more than 16 tile bits fall back to the histogram kernel
+    const int bits0 = (tbits > 8) ? (tbits + 1) / 2 : tbits;
+    const bool scan_hist = (tbits <= 16) && !keys64;
+    SplatBuffers sp = h->sp;
+    sp.tile_grid = h->d_tile_grid;
+    sp.grid_w = h->grid_w;
+    sp.grid_stride = h->grid_w * (h->tiles_y + 1);
 
     if (timed) cudaEventRecord(h->ev[0], s);
     launch_set_params(h->d_fp, fp, h->d_counters, s);
-    launch_preprocess(h->d_fp, scene, h->sp, h->d_counters, N, h->sh_dim, s);
+    CK(cudaMemsetAsync(h->d_tile_grid, 0, sizeof(int) * (size_t)sp.grid_stride * GSR_GRID_REPLICAS, s));
+    launch_preprocess(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     h->launches += 2;
     if (timed) cudaEventRecord(h->ev[1], s);
     CK(cudaMemsetAsync(h->d_chain, 0, h->chain_bytes, s));
     uint32_t* chain_ticket = reinterpret_cast<uint32_t*>(h->d_chain + (h->chain_bytes / 8 - 1));
+    const uint32_t* n_sort = &h->d_counters->n_sort;
     int res = 0;
     if (!keys64) {
         // depth sort of the N Gaussians (culled ones carry key 0xFFFFFFFF and sort to the end)
@@ -209,28 +221,36 @@ int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bo
                                                   true, N, nullptr, N, 0, 32, &h->ss_n, s, &h->launches);
         const uint32_t* sorted_gid = h->d_gid[r0];
         if (timed) cudaEventRecord(h->ev[2], s);
-        launch_duplicate_sorted(h->d_fp, sorted_gid, h->sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain),
+        // counts -> ranges, D, overflow flag, digit histograms of the tile sort
+        launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges, h->ss_i.hist,
+                         h->d_counters, s);
+        h->launches += 1;
+        if (timed) cudaEventRecord(h->ev[3], s);
+        launch_duplicate_sorted(h->d_fp, sorted_gid, sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain),
                                 chain_ticket, (uint32_t*)h->d_ikeys[0], h->d_ivals[0], nullptr, N, cap, s);
         h->launches += 1;
-        if (timed) cudaEventRecord(h->ev[3], s);
-        res = radix_sort_pairs<uint32_t>((uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[1],
-                                         h->d_ivals[0], h->d_ivals[1], false, 0, n_inst, cap, 0, tbits, &h->ss_i, s,
-                                         &h->launches);
         if (timed) cudaEventRecord(h->ev[4], s);
-        launch_tile_ranges<uint32_t>((const uint32_t*)h->d_ikeys[res], 0, h->d_counters, cap, h->d_ranges, n_tiles, s);
+        SortOptions so = {scan_hist ? bits0 : 0, scan_hist, true};
+        res = radix_sort_pairs<uint32_t>((uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[1],
+                                         h->d_ivals[0], h->d_ivals[1], false, 0, n_sort, cap, 0, tbits, &h->ss_i, s,
+                                         &h->launches, &so);
     } else {
         if (timed) cudaEventRecord(h->ev[2], s);
-        launch_duplicate_keys64(h->d_fp, h->sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain), chain_ticket,
-                                (uint64_t*)h->d_ikeys[0], h->d_ivals[0], N, cap, s);
+        launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges, h->ss_i.hist,
+                         h->d_counters, s);
         h->launches += 1;
         if (timed) cudaEventRecord(h->ev[3], s);
-        res = radix_sort_pairs<uint64_t>((uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[1],
-                                         h->d_ivals[0], h->d_ivals[1], false, 0, n_inst, cap, 0, 32 + tbits, &h->ss_i, s,
-                                         &h->launches);
+        launch_duplicate_keys64(h->d_fp, sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain), chain_ticket,
+                                (uint64_t*)h->d_ikeys[0], h->d_ivals[0], N, cap, s);
+        h->launches += 1;
         if (timed) cudaEventRecord(h->ev[4], s);
+        res = radix_sort_pairs<uint64_t>((uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[1],
+                                         h->d_ivals[0], h->d_ivals[1], false, 0, n_sort, cap, 0, 32 + tbits, &h->ss_i, s,
+                                         &h->launches);
+        // the one-sort variant re-derives the ranges from the sorted keys (cross-check of k_tile_scan)
         launch_tile_ranges<uint64_t>((const uint64_t*)h->d_ikeys[res], 32, h->d_counters, cap, h->d_ranges, n_tiles, s);
+        h->launches += 1;
     }
-    h->launches += 1;
     if (timed) cudaEventRecord(h->ev[5], s);
     launch_blend(h->d_fp, h->d_ranges, h->d_ivals[res], h->sp, out, fp.render_mod, fp.flags, h->tiles_x, h->tiles_y, s);
     h->launches += 1;
@@ -309,7 +329,7 @@ int gsr_destroy(gsr_t* h) {
     cudaDeviceSynchronize();
     free_gaussian_buffers(h);
     free_instance_buffers(h);
-    dfree(h->d_ranges); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
+    dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
     dfree(h->d_fp); dfree(h->d_counters); dfree(h->d_sortp);
     if (h->h_counters) cudaFreeHost(h->h_counters);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
@@ -375,12 +395,14 @@ int gsr_set_resolution(gsr_t* h, int width, int height) {
     CK(cudaSetDevice(h->device));
     if (width == h->W && height == h->H) return 0;
     CK(cudaDeviceSynchronize());
-    dfree(h->d_ranges); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
+    dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
     h->W = width; h->H = height;
     h->tiles_x = (width + GSR_TILE - 1) / GSR_TILE;
     h->tiles_y = (height + GSR_TILE - 1) / GSR_TILE;
     const size_t npx = (size_t)width * height;
     CK(cudaMalloc(&h->d_ranges, sizeof(int2) * (size_t)h->tiles_x * h->tiles_y));
+    h->grid_w = (h->tiles_x + 1) | 1;  // odd pitch: conflict-free column walks in k_tile_scan
+    CK(cudaMalloc(&h->d_tile_grid, sizeof(int) * (size_t)h->grid_w * (h->tiles_y + 1) * GSR_GRID_REPLICAS));
     CK(cudaMalloc(&h->d_frame, npx * 16));
     CK(cudaMalloc(&h->d_rgb8, npx * 3));
     CK(cudaMalloc(&h->d_r32, npx * 4));
@@ -442,9 +464,9 @@ int gsr_render_timed(gsr_t* h, float* out_rgba, void* stream) {
     for (int i = 0; i < 6; ++i) CK(cudaEventElapsedTime(&ms[i], h->ev[i], h->ev[i + 1]));
     h->stats.ms_preprocess = ms[0];
     h->stats.ms_sort_depth = ms[1];
-    h->stats.ms_duplicate = ms[2];
-    h->stats.ms_sort_tiles = ms[3];
-    h->stats.ms_ranges = ms[4];
+    h->stats.ms_ranges = ms[2];  // k_tile_scan: counts -> ranges + sort histograms
+    h->stats.ms_duplicate = ms[3];
+    h->stats.ms_sort_tiles = ms[4];
     h->stats.ms_blend = ms[5];
     CK(cudaEventElapsedTime(&h->stats.ms_total, h->ev[0], h->ev[6]));
     return 0;
@@ -584,8 +606,8 @@ int gsr_debug_fetch(gsr_t* h, int which, void* dst, long long capacity_bytes, lo
             else if (D > 0 && dst) {
                 dfree(h->d_dbgkeys);
                 CK(cudaMalloc(&h->d_dbgkeys, (size_t)D * 8));
-                launch_keys64_from_sorted((const uint32_t*)h->d_ikeys[h->last_result_buf], h->d_ivals[h->last_result_buf],
-                                          h->sp.depth_key, h->d_counters, h->capacity, h->d_dbgkeys, 0);
+                launch_keys64_from_ranges(h->d_ranges, h->tiles_x * h->tiles_y, h->d_ivals[h->last_result_buf],
+                                          h->sp.depth_key, h->d_dbgkeys, 0);
                 CK(cudaDeviceSynchronize());
                 src = h->d_dbgkeys;
             }
@@ -618,6 +640,9 @@ int gsr_tune(gsr_t* h, int key, int value) {
             if (value != 1 && value != 2 && value != 4) return fail(GSR_EINVAL, "blend ppt must be 1, 2 or 4");
             set_blend_ppt(value);
             return 0;
+        case GSR_TUNE_BLEND_SHAPE8: set_blend_shape8(value); return 0;
+        case GSR_TUNE_BLEND_SKIP: set_blend_skip(value); return 0;
+        case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;
         default: return fail(GSR_EINVAL, "unknown tuning key");
     }
 }

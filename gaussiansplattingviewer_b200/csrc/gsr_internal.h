@@ -3,7 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#define GSR_TILE 16  // pixels per tile edge (16x16 tiles, one CTA per tile in the blend kernel)
+#define GSR_TILE 16
+#define GSR_GRID_REPLICAS 16  // copies of the corner-impulse grid (CTA b adds into copy b % 16)  // pixels per tile edge (16x16 tiles, one CTA per tile in the blend kernel)
 
 // Per-frame uniforms.  Lives in device memory (written by k_set_params) so that a captured CUDA graph
 // can be replayed with a new camera by updating one kernel node.
@@ -25,7 +26,7 @@ struct FrameCounters {
     unsigned n_visible;    // Gaussians with ok = 1
     unsigned n_instances;  // D (sum of tiles touched), unclamped
     unsigned overflow;     // D > capacity
-    unsigned pad;
+    unsigned n_sort;       // instances the tile sort handles: D, or 0 when the buffers overflowed
 };
 
 // Splat record, three float4 planes indexed by Gaussian:
@@ -46,6 +47,9 @@ struct SplatBuffers {
     float4* rec2;
     uint32_t* depth_key;  // bits(depth) or 0xFFFFFFFF when not ok
     uint2* trect;         // tile rectangle (0 x 0 when not ok)
+    int* tile_grid;       // (tiles_y + 1) x grid_w corner impulses of the tile rectangles (see k_tile_scan)
+    int grid_w;           // row pitch of tile_grid: tiles_x + 1 rounded up to an odd number
+    int grid_stride;      // ints per replica; GSR_GRID_REPLICAS replicas spread the atomics of hot tiles
     float* dbg_vsout;     // N x 16 or nullptr
     int32_t* dbg_setup;   // N x 8 or nullptr
 };
@@ -69,10 +73,20 @@ void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key
 // scratch->hist by a producer kernel (skip the histogram kernel and the clear).
 // keys_first: input of the first pass (may equal keys; it is only read), so a key array can be sorted
 // without being overwritten.
+// opt (may be nullptr): first_bits = width of the first digit (0 = 8; later digits are 8 bits wide);
+// hist_ready = scratch->hist already holds the per-pass digit counts (k_tile_scan), skip the histogram
+// kernel; vals_only_last = the last pass does not write keys (the caller only needs the permuted values).
+struct SortOptions {
+    int first_bits;
+    bool hist_ready;
+    bool vals_only_last;
+};
 template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
                      long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
-                     SortScratch* scratch, cudaStream_t stream, long long* launch_count);
+                     SortScratch* scratch, cudaStream_t stream, long long* launch_count, const SortOptions* opt = nullptr);
+void launch_tile_scan(int* grid, int grid_stride, int gw, int tiles_x, int tiles_y, int bits0, long long capacity, int2* ranges,
+                      uint32_t* hist, FrameCounters* counters, cudaStream_t s);
 
 // ---- kernels' host launchers ---------------------------------------------------------------------
 void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s);
@@ -95,10 +109,13 @@ void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* ins
                   float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s);
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s);
 void launch_extract_r(const float* rgba, float* r, long long n_px, cudaStream_t s);
-void launch_keys64_from_sorted(const uint32_t* tile_keys, const uint32_t* gid, const uint32_t* depth_key,
-                               const FrameCounters* counters, long long capacity, uint64_t* out, cudaStream_t s);
+void launch_keys64_from_ranges(const int2* ranges, int n_tiles, const uint32_t* gid, const uint32_t* depth_key,
+                               uint64_t* out, cudaStream_t s);
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                         float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
                         unsigned long long* pair_counts, cudaStream_t s);
 void set_blend_ppt(int v);
+void set_blend_shape8(int v);
+void set_blend_skip(int v);
+void set_sort_small_tiles(int v);
 int measure_peaks_impl(float* fp32_tflops, float* ex2_tops, float* copy_gbs);

@@ -87,7 +87,7 @@ struct SharedParams {
     float htanx, htany, focal;
     float campos[3];
     float scale_modifier;
-    int render_mod, W, H, tiles_x;
+    int render_mod, W, H, tiles_x, tiles_y;
     unsigned flags;
 };
 
@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
         P.htanx = fp->htanx; P.htany = fp->htany; P.focal = fp->focal;
         P.campos[0] = fp->campos[0]; P.campos[1] = fp->campos[1]; P.campos[2] = fp->campos[2];
         P.scale_modifier = fp->scale_modifier; P.render_mod = fp->render_mod;
-        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.flags = fp->flags;
+        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.tiles_y = fp->tiles_y; P.flags = fp->flags;
         s_visible = 0;
     }
     __syncthreads();
@@ -267,6 +267,17 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
             const int tx0 = imin / GSR_TILE, tx1 = imax / GSR_TILE, ty0 = jmin / GSR_TILE, ty1 = jmax / GSR_TILE;
             trect.x = (unsigned)tx0 | ((unsigned)(tx1 - tx0 + 1) << 16);
             trect.y = (unsigned)ty0 | ((unsigned)(ty1 - ty0 + 1) << 16);
+            // per-tile instance counts without one atomic per tile: the rectangle is the 2D prefix sum of four
+            // corner impulses (+1, -1, -1, +1); k_tile_scan integrates the grid into counts, list offsets
+            // and the digit histograms of the tile sort
+            if (out.tile_grid) {
+                const int gw = out.grid_w;
+                int* grid = out.tile_grid + (size_t)(blockIdx.x & (GSR_GRID_REPLICAS - 1)) * out.grid_stride;
+                atomicAdd(grid + ty0 * gw + tx0, 1);
+                atomicAdd(grid + ty0 * gw + (tx1 + 1), -1);
+                atomicAdd(grid + (ty1 + 1) * gw + tx0, -1);
+                atomicAdd(grid + (ty1 + 1) * gw + (tx1 + 1), 1);
+            }
             // source-colour clamp of a normalised target (ref_driver.inc); mode -4 scales the colour per
             // fragment first, so only the lower clamp can be applied here
             if (P.flags & 1u) {
@@ -308,7 +319,7 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
 __global__ void k_set_params(FrameParams* dst, FrameParams fp, FrameCounters* counters) {
     if (threadIdx.x == 0) {
         *dst = fp;
-        if (counters) { counters->n_visible = 0; counters->n_instances = 0; counters->overflow = 0; counters->pad = 0; }
+        if (counters) { counters->n_visible = 0; counters->n_instances = 0; counters->overflow = 0; counters->n_sort = 0; }
     }
 }
 

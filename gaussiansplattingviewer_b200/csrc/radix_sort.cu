@@ -27,9 +27,12 @@ constexpr uint32_t RS_FLAG_INC = 2u << 30;
 constexpr uint32_t RS_FLAG_MASK = 3u << 30;
 constexpr uint32_t RS_VAL_MASK = (1u << 30) - 1u;
 
+// items per thread of the scatter pass: LARGE is the default, SMALL trades tile size for occupancy
+// (48 registers, 5 CTAs per SM); gsr_tune(GSR_TUNE_SORT_ITEMS) switches between them
 template <typename KeyT> struct RsCfg;
-template <> struct RsCfg<uint32_t> { static constexpr int ITEMS = 16; };
-template <> struct RsCfg<uint64_t> { static constexpr int ITEMS = 12; };
+template <> struct RsCfg<uint32_t> { static constexpr int LARGE = 16, SMALL = 8; };
+template <> struct RsCfg<uint64_t> { static constexpr int LARGE = 12, SMALL = 6; };
+int g_rs_small = 0;
 
 struct RsPasses {
     int n;
@@ -96,7 +99,7 @@ template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const KeyT* __restrict__ keys, long long n_host,
                                                        const uint32_t* __restrict__ n_dev, long long capacity,
                                                        RsPasses passes, uint32_t* __restrict__ hist,
-                                                       uint32_t* __restrict__ status0) {
+                                                       uint32_t* __restrict__ status0, int tile_items) {
     __shared__ uint32_t s_hist[8 * 256];
     long long n = n_dev ? (long long)(*n_dev) : n_host;
     if (n > capacity) n = capacity;
@@ -144,20 +147,18 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const KeyT* __restrict__
         if (c) atomicAdd(&hist[i], c);
     }
     // clear the look-back rows the first pass will use
-    constexpr int TILE = RS_THREADS * RsCfg<KeyT>::ITEMS;
-    const long long rows = (n + TILE - 1) / TILE;
+    const long long rows = (n + tile_items - 1) / tile_items;
     for (long long i = (long long)blockIdx.x * RS_THREADS + threadIdx.x; i < rows * 256; i += stride) status0[i] = 0;
 }
 
-template <typename KeyT, bool IDENTITY_VALS>
-__global__ void __launch_bounds__(RS_THREADS) k_rs_pass(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
+template <typename KeyT, int ITEMS, bool IDENTITY_VALS>
+__global__ void __launch_bounds__(RS_THREADS, (ITEMS <= 8 ? 5 : 3)) k_rs_pass(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out,
                                                        const uint32_t* __restrict__ vals_in,
                                                        uint32_t* __restrict__ vals_out, long long n_host,
                                                        const uint32_t* __restrict__ n_dev, long long capacity,
                                                        int shift, int bits, const uint32_t* __restrict__ hist,
                                                        uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_cur,
                                                        uint32_t* __restrict__ status_next) {
-    constexpr int ITEMS = RsCfg<KeyT>::ITEMS;
     constexpr int TILE = RS_THREADS * ITEMS;
     __shared__ KeyT s_keys[TILE];
     __shared__ uint32_t s_vals[TILE];
@@ -257,7 +258,7 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_pass(const KeyT* __restrict__
             const KeyT k = s_keys[s];
             const uint32_t d = (uint32_t)(k >> shift) & mask;
             const uint32_t dst = s_bin_base[d] + (uint32_t)s;
-            keys_out[dst] = k;
+            if (keys_out) keys_out[dst] = k;  // nullptr: the caller only needs the permuted values (last pass)
             vals_out[dst] = s_vals[s];
         }
         __syncthreads();
@@ -277,14 +278,16 @@ int num_sms() {
 
 }  // namespace
 
+void set_sort_small_tiles(int v) { g_rs_small = v ? 1 : 0; }
+
 size_t sort_scratch_bytes(long long max_items, int key_bytes) {
-    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::ITEMS : RsCfg<uint32_t>::ITEMS;
+    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::SMALL : RsCfg<uint32_t>::SMALL;
     const long long tiles = (max_items + RS_THREADS * items - 1) / (RS_THREADS * items) + 1;
     return (size_t)(8 * 256 + 64) * 4 + 2 * (size_t)tiles * 256 * 4;
 }
 
 void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key_bytes) {
-    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::ITEMS : RsCfg<uint32_t>::ITEMS;
+    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::SMALL : RsCfg<uint32_t>::SMALL;
     const long long tiles = (max_items + RS_THREADS * items - 1) / (RS_THREADS * items) + 1;
     uint32_t* p = reinterpret_cast<uint32_t*>(base);
     s->hist = p;
@@ -295,50 +298,74 @@ void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key
     s->max_tiles = tiles;
 }
 
+template <typename KeyT, int ITEMS>
+void launch_pass(bool identity, unsigned grid, cudaStream_t stream, const KeyT* kin, KeyT* kout, const uint32_t* vin,
+                 uint32_t* vout, long long n_host, const uint32_t* n_dev, long long capacity, int shift, int bits,
+                 const uint32_t* hist, uint32_t* ticket, uint32_t* st_cur, uint32_t* st_next) {
+    if (identity)
+        k_rs_pass<KeyT, ITEMS, true><<<grid, RS_THREADS, 0, stream>>>(kin, kout, nullptr, vout, n_host, n_dev, capacity, shift,
+                                                                     bits, hist, ticket, st_cur, st_next);
+    else
+        k_rs_pass<KeyT, ITEMS, false><<<grid, RS_THREADS, 0, stream>>>(kin, kout, vin, vout, n_host, n_dev, capacity, shift,
+                                                                      bits, hist, ticket, st_cur, st_next);
+}
+
 template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
                      long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
-                     SortScratch* scratch, cudaStream_t stream, long long* launch_count) {
+                     SortScratch* scratch, cudaStream_t stream, long long* launch_count, const SortOptions* opt) {
+    const int first_bits = (opt && opt->first_bits > 0) ? opt->first_bits : 8;
+    const bool hist_ready = opt && opt->hist_ready;
+    const bool vals_only_last = opt && opt->vals_only_last;
     RsPasses passes;
     passes.n = 0;
-    for (int b = begin_bit; b < end_bit && passes.n < 8; b += 8) {
+    for (int b = begin_bit; b < end_bit && passes.n < 8;) {
+        const int want = (passes.n == 0) ? first_bits : 8;
         passes.shift[passes.n] = b;
-        passes.bits[passes.n] = (end_bit - b < 8) ? (end_bit - b) : 8;
+        passes.bits[passes.n] = (end_bit - b < want) ? (end_bit - b) : want;
+        b += passes.bits[passes.n];
         ++passes.n;
     }
     for (int p = passes.n; p < 8; ++p) { passes.shift[p] = 0; passes.bits[p] = 1; }
     if (passes.n == 0) return 0;
     const long long upper = n_dev ? capacity : n_host;
     if (upper <= 0) return 0;
-    cudaMemsetAsync(scratch->hist, 0, scratch->zero_bytes, stream);
-    constexpr int TILE = RS_THREADS * RsCfg<KeyT>::ITEMS;
+    const bool small = g_rs_small != 0;
+    const int TILE = RS_THREADS * (small ? RsCfg<KeyT>::SMALL : RsCfg<KeyT>::LARGE);
     const long long tiles_upper = (upper + TILE - 1) / TILE;
     const int sms = num_sms();
-    {
+    if (hist_ready) {
+        // the digit histograms were produced by the caller (k_tile_scan): clear the tickets and the
+        // look-back rows of the first pass only
+        cudaMemsetAsync(scratch->tickets, 0, 64 * sizeof(uint32_t), stream);
+        cudaMemsetAsync(scratch->status[0], 0, (size_t)tiles_upper * 256 * sizeof(uint32_t), stream);
+    } else {
+        cudaMemsetAsync(scratch->hist, 0, scratch->zero_bytes, stream);
         long long g = (upper + RS_THREADS * 8 - 1) / (RS_THREADS * 8);
         if (g > sms * 8) g = sms * 8;
         if (g < 1) g = 1;
         k_rs_hist<KeyT><<<(unsigned)g, RS_THREADS, 0, stream>>>(keys_first, n_host, n_dev, capacity, passes, scratch->hist,
-                                                               scratch->status[0]);
+                                                               scratch->status[0], TILE);
         if (launch_count) ++*launch_count;
     }
-    long long grid = tiles_upper < (long long)sms * 4 ? tiles_upper : (long long)sms * 4;
+    const int per_sm = small ? 5 : 3;  // resident CTAs per SM (registers): persistent CTAs, one wave
+    long long grid = tiles_upper < (long long)sms * per_sm ? tiles_upper : (long long)sms * per_sm;
     if (grid < 1) grid = 1;
     const KeyT* kin = keys_first; KeyT* kout = keys_tmp; KeyT* kother = keys;
     uint32_t* vin = vals; uint32_t* vout = vals_tmp;
     for (int p = 0; p < passes.n; ++p) {
+        if (vals_only_last && p == passes.n - 1) kout = nullptr;
         uint32_t* st_cur = scratch->status[p & 1];
         uint32_t* st_next = scratch->status[(p + 1) & 1];
-        if (p == 0 && vals_identity)
-            k_rs_pass<KeyT, true><<<(unsigned)grid, RS_THREADS, 0, stream>>>(kin, kout, nullptr, vout, n_host, n_dev, capacity,
-                                                                            passes.shift[p], passes.bits[p],
-                                                                            scratch->hist + p * 256, scratch->tickets + p,
-                                                                            st_cur, st_next);
+        const bool identity = (p == 0 && vals_identity);
+        if (small)
+            launch_pass<KeyT, RsCfg<KeyT>::SMALL>(identity, (unsigned)grid, stream, kin, kout, vin, vout, n_host, n_dev, capacity,
+                                                  passes.shift[p], passes.bits[p], scratch->hist + p * 256,
+                                                  scratch->tickets + p, st_cur, st_next);
         else
-            k_rs_pass<KeyT, false><<<(unsigned)grid, RS_THREADS, 0, stream>>>(kin, kout, vin, vout, n_host, n_dev, capacity,
-                                                                             passes.shift[p], passes.bits[p],
-                                                                             scratch->hist + p * 256, scratch->tickets + p,
-                                                                             st_cur, st_next);
+            launch_pass<KeyT, RsCfg<KeyT>::LARGE>(identity, (unsigned)grid, stream, kin, kout, vin, vout, n_host, n_dev, capacity,
+                                                  passes.shift[p], passes.bits[p], scratch->hist + p * 256,
+                                                  scratch->tickets + p, st_cur, st_next);
         if (launch_count) ++*launch_count;
         kin = kout; { KeyT* tk = kout; kout = kother; kother = tk; }
         uint32_t* tv = vin; vin = vout; vout = tv;
@@ -347,6 +374,6 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
 }
 
 template int radix_sort_pairs<uint32_t>(const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, bool, long long, const uint32_t*,
-                                        long long, int, int, SortScratch*, cudaStream_t, long long*);
+                                        long long, int, int, SortScratch*, cudaStream_t, long long*, const SortOptions*);
 template int radix_sort_pairs<uint64_t>(const uint64_t*, uint64_t*, uint64_t*, uint32_t*, uint32_t*, bool, long long, const uint32_t*,
-                                        long long, int, int, SortScratch*, cudaStream_t, long long*);
+                                        long long, int, int, SortScratch*, cudaStream_t, long long*, const SortOptions*);

@@ -145,8 +145,12 @@ int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy
 int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed);
 
 /* Kernel-variant knobs for measurement runs (process-wide; results are identical for every setting).
- * GSR_TUNE_BLEND_PPT: pixels per thread of the blend kernel, 1, 2 or 4. */
+ * GSR_TUNE_BLEND_PPT: pixels per thread of the blend kernel, 1, 2 or 4.
+ * GSR_TUNE_SORT_SMALL_TILES: 1 = radix passes use 2048-item tiles at 5 CTAs/SM instead of 4096 at 3. */
 #define GSR_TUNE_BLEND_PPT 0
+#define GSR_TUNE_SORT_SMALL_TILES 1
+#define GSR_TUNE_BLEND_SHAPE8 2 /* 1 = a warp owns an 8-column block instead of 16 columns (main mode only) */
+#define GSR_TUNE_BLEND_SKIP 3   /* 1 = warp-level skip of quads that miss all of the warp's live pixels */
 int gsr_tune(gsr_t* h, int key, int value);
 
 #ifdef __cplusplus
