@@ -22,6 +22,7 @@ GSR_TUNE_BLEND_PPT = 0
 GSR_TUNE_SORT_SMALL_TILES = 1
 GSR_TUNE_BLEND_SHAPE8 = 2
 GSR_TUNE_BLEND_SKIP = 3
+GSR_TUNE_SORT_PREFETCH = 4
 
 
 class Stats(C.Structure):

@@ -5,10 +5,11 @@
 //     path, index order for the 64-bit-key path), block-scans their tile counts, chains the chunk total
 //     to the previous chunks with a decoupled look-back (64-bit status word: 2 flag bits + count), so the
 //     prefix sum never makes a round trip through global memory;
-//   * instances are emitted warp-cooperatively: a warp walks its 128 Gaussians, broadcasts one
-//     rectangle at a time with shuffles and its 32 lanes write that Gaussian's instances (tile index by
-//     a multiply-high with a per-Gaussian magic reciprocal, no division, no search), so stores are
-//     contiguous runs; rectangles above DUP_BIG tiles are deferred and written by the whole CTA.
+//   * instances are emitted warp-cooperatively and load balanced over instances: lane l of a warp writes
+//     output slot s * 32 + l of the warp's current 32 Gaussians and finds the owning Gaussian with a
+//     5-step binary search over the lanes' offsets (shuffles); the tile index comes from a multiply-high
+//     with a per-Gaussian magic reciprocal (no division); stores are contiguous.  Rectangles above
+//     DUP_BIG tiles are deferred and written by the whole CTA.
 // Counterpart of the scan + duplicateWithKeys + identifyTileRanges steps of the tile rasteriser the
 // reference's CUDA backend calls (/root/reference/renderer_cuda.py:211-224); the OpenGL backend has no
 // tiles (its draw is one instanced quad per Gaussian, renderer_ogl.py:175-179).
@@ -153,23 +154,42 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
         }
         __syncthreads();
         const unsigned long long prefix = s_prefix;
-        // ---- warp-cooperative emission
+        // ---- warp-cooperative emission, load balanced over INSTANCES: in each round the 32 Gaussians of the
+        // warp (one per lane) own consecutive runs of the round's output; lane l of step s writes output
+        // s * 32 + l and finds its owner by a 5-step binary search over the lanes' offsets (shuffles), so all
+        // 32 lanes store no matter how small the rectangles are (one Gaussian per step kept 24 % of the
+        // lanes busy at 7.6 tiles per Gaussian)
 #pragma unroll
         for (int i = 0; i < DUP_ITEMS; ++i) {
-            uint32_t todo = __ballot_sync(0xffffffffu, cnt[i] != 0u);
-            while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1u;
-                const uint32_t o = __shfl_sync(0xffffffffu, off[i], src);
-                const uint32_t x = __shfl_sync(0xffffffffu, rx[i], src);
-                const uint32_t y = __shfl_sync(0xffffffffu, ry[i], src);
-                const uint32_t g = __shfl_sync(0xffffffffu, gid[i], src);
-                const uint32_t m = __shfl_sync(0xffffffffu, magic[i], src);
-                const uint32_t w = x >> 16, c = w * (y >> 16);
-                const uint32_t tile0 = (y & 0xFFFFu) * tiles_x + (x & 0xFFFFu);
-                for (uint32_t k = lane; k < c; k += 32) {
-                    const uint32_t row = div_magic(k, w, m, true);  // c <= DUP_BIG < 65536
-                    emit(prefix + o + k, tile0 + row * tiles_x + (k - row * w), g);
+            // offsets of the round without the deferred rectangles
+            uint32_t incl = cnt[i];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const uint32_t oloc = incl - cnt[i];
+            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+            for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+                const uint32_t j = j0 + lane;
+                int pos = 0;
+#pragma unroll
+                for (int step = 16; step > 0; step >>= 1) {
+                    const int c = pos + step;
+                    const uint32_t v = __shfl_sync(0xffffffffu, oloc, c & 31);
+                    if (c < 32 && v <= j) pos = c;
+                }
+                const uint32_t ol = __shfl_sync(0xffffffffu, oloc, pos);
+                const uint32_t ot = __shfl_sync(0xffffffffu, off[i], pos);
+                const uint32_t x = __shfl_sync(0xffffffffu, rx[i], pos);
+                const uint32_t y = __shfl_sync(0xffffffffu, ry[i], pos);
+                const uint32_t g = __shfl_sync(0xffffffffu, gid[i], pos);
+                const uint32_t m = __shfl_sync(0xffffffffu, magic[i], pos);
+                if (j < total) {
+                    const uint32_t k = j - ol;
+                    const uint32_t w = x >> 16;
+                    const uint32_t row = div_magic(k, w, m, true);  // rectangle <= DUP_BIG < 65536 instances
+                    emit(prefix + ot + k, (y & 0xFFFFu) * tiles_x + (x & 0xFFFFu) + row * tiles_x + (k - row * w), g);
                 }
             }
         }

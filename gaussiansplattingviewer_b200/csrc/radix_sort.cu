@@ -33,6 +33,7 @@ template <typename KeyT> struct RsCfg;
 template <> struct RsCfg<uint32_t> { static constexpr int LARGE = 16, SMALL = 8; };
 template <> struct RsCfg<uint64_t> { static constexpr int LARGE = 12, SMALL = 6; };
 int g_rs_small = 0;
+int g_rs_prefetch = 1;
 
 struct RsPasses {
     int n;
@@ -52,17 +53,61 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t* p, uint32_t v) {
 // Lanes of the warp whose digit equals this lane's.  Built from one ballot per digit bit: the hardware
 // MATCH.ANY instruction runs on the address-divergence unit at a fraction of ALU rate (ncu: pipe_adu 85 %
 // in the histogram kernel, 72 % in the scatter pass), VOTE + LOP3 run at full rate.
-__device__ __forceinline__ uint32_t match_digit(uint32_t d, int bits) {
+__device__ __forceinline__ uint32_t match_digit(uint32_t d, int /*bits*/) {
     uint32_t peers = 0xffffffffu;
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
-        if (b < bits) {  // warp-uniform
-            const bool bit = (d >> b) & 1u;
-            const uint32_t m = __ballot_sync(0xffffffffu, bit);
-            peers &= bit ? m : ~m;
-        }
+        // all 8 bits always: digits are masked to `bits` bits, so the upper ballots agree on every lane and
+        // cost less than predicating each step on a run-time bit count.  Four instructions per bit:
+        // LOP3 -> predicate, VOTE, and one of two predicated LOP3s.
+        asm("{\n\t"
+            ".reg .pred p;\n\t"
+            ".reg .b32 t, m;\n\t"
+            "and.b32 t, %1, %2;\n\t"
+            "setp.ne.b32 p, t, 0;\n\t"
+            "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+            "@p and.b32 %0, %0, m;\n\t"
+            "@!p lop3.b32 %0, %0, m, 0, 0x30;\n\t"
+            "}"
+            : "+r"(peers)
+            : "r"(d), "r"(1u << b));
     }
     return peers;
+}
+
+// Decoupled look-back for digit t of tile `tile`: sum of the counts of all earlier tiles.  Walks back over
+// the per-tile status words until one carries an inclusive prefix.  The walk must outrun the rate at which
+// new tiles are started (hundreds of CTAs are in flight and none of the tiles right behind this one has an
+// inclusive prefix yet): a walk of one dependent L2 read per step left 40 % of the pass waiting here
+// (clock64 phase timing), so WIN status words are fetched per round trip - 4 first (the usual case ends
+// there), then 16 at a time.
+template <int WIN>
+__device__ __forceinline__ bool look_back_round(const uint32_t* status, long long& p, int t, uint32_t& prefix) {
+    uint32_t w[WIN];
+#pragma unroll
+    for (int k = 0; k < WIN; ++k) w[k] = (p - k >= 0) ? ld_volatile_u32(&status[(p - k) * 256 + t]) : RS_FLAG_INC;
+    bool done = false;
+    int used = 0;
+#pragma unroll
+    for (int k = 0; k < WIN; ++k) {
+        if (!done && used == k && (w[k] & RS_FLAG_MASK) != 0u) {
+            prefix += w[k] & RS_VAL_MASK;
+            used = k + 1;
+            if (w[k] & RS_FLAG_INC) done = true;
+        }
+    }
+    p -= used;
+    // nothing new since the last probe: back off instead of spinning - the CTAs sharing this SM are
+    // ranking their tiles and need the issue slots (ALU pipe) this loop would burn
+    if (!done && used == 0) __nanosleep(256);
+    return done;
+}
+__device__ __forceinline__ uint32_t look_back(const uint32_t* status, long long tile, int t) {
+    uint32_t prefix = 0;
+    long long p = tile - 1;
+    if (look_back_round<4>(status, p, t, prefix)) return prefix;
+    while (!look_back_round<16>(status, p, t, prefix)) {}
+    return prefix;
 }
 
 // exclusive scan of one value per thread over a 256-thread block; returns the exclusive prefix and the
@@ -228,18 +273,14 @@ __global__ void __launch_bounds__(RS_THREADS, (ITEMS <= 8 ? 5 : 3)) k_rs_pass(co
         }
         // padding keys (all ones) sit in digit `mask`, after every valid key of that digit
         const uint32_t count_pub = count - (((uint32_t)t == mask) ? (uint32_t)(TILE - n_valid) : 0u);
-        st_volatile_u32(&status_cur[tile * 256 + t], ((tile == 0) ? RS_FLAG_INC : RS_FLAG_AGG) | count_pub);
+        if ((uint32_t)t <= mask)  // digits above the mask do not exist in this pass
+            st_volatile_u32(&status_cur[tile * 256 + t], ((tile == 0) ? RS_FLAG_INC : RS_FLAG_AGG) | count_pub);
         const uint32_t dstart = block_excl_scan_256(count, s_tmp, nullptr);
         s_digit_start[t] = dstart;
         // ---- decoupled look-back over previous tiles for digit t
         uint32_t prefix = 0;
-        if (tile > 0) {
-            for (long long p = tile - 1;; --p) {
-                uint32_t w;
-                do { w = ld_volatile_u32(&status_cur[p * 256 + t]); } while ((w & RS_FLAG_MASK) == 0u);
-                prefix += w & RS_VAL_MASK;
-                if (w & RS_FLAG_INC) break;
-            }
+        if (tile > 0 && (uint32_t)t <= mask) {
+            prefix = look_back(status_cur, tile, t);
             st_volatile_u32(&status_cur[tile * 256 + t], RS_FLAG_INC | (prefix + count_pub));
         }
         s_bin_base[t] = s_global_excl[t] + prefix - dstart;
@@ -265,6 +306,150 @@ __global__ void __launch_bounds__(RS_THREADS, (ITEMS <= 8 ? 5 : 3)) k_rs_pass(co
     }
 }
 
+// ---- k_rs_pass2: the same pass over SUPER-TILES of S sub-tiles ------------------------------------
+// clock64 phase timing of k_rs_pass showed 40 % of a pass waiting in the look-back: the persistent CTAs
+// run in lock step, so in every wave the inclusive prefix has to cross all ~444 tiles in flight before the
+// last of them can write, and that chain repeats every wave.  Its total length is (tiles) / sqrt(tiles
+// in flight), so the cure is fewer, larger tiles without fewer CTAs: a CTA ranks S sub-tiles one after
+// the other, parks each one tile-sorted in shared memory (the registers are free again for the next),
+// publishes ONE count row for all of them and does ONE look-back.  S = 2 uses the shared memory three
+// CTAs per SM can have (2 x 32 KB staging each) and halves the chain.
+template <int ITEMS, int S, bool IDENTITY_VALS>
+__global__ void __launch_bounds__(RS_THREADS, 3) k_rs_pass2(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
+                                                          const uint32_t* __restrict__ vals_in,
+                                                          uint32_t* __restrict__ vals_out, long long n_host,
+                                                          const uint32_t* __restrict__ n_dev, long long capacity,
+                                                          int shift, int bits, const uint32_t* __restrict__ hist,
+                                                          uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_cur,
+                                                          uint32_t* __restrict__ status_next) {
+    constexpr int TILE = RS_THREADS * ITEMS;  // one sub-tile
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    uint32_t* s_keys = reinterpret_cast<uint32_t*>(s_dyn);  // [S][TILE] tile-sorted keys
+    uint32_t* s_vals = s_keys + S * TILE;                   // [S][TILE]
+    __shared__ uint16_t s_whist[RS_WARPS][256];  // per-warp digit counts (<= 32 * ITEMS each)
+    __shared__ uint32_t s_digit_start[256];
+    __shared__ uint32_t s_bin_base[S][256];
+    __shared__ uint32_t s_global_excl[256];
+    __shared__ uint32_t s_tmp[RS_WARPS + 1];
+    __shared__ uint32_t s_tile;
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const uint32_t mask = (1u << bits) - 1u;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    long long n = n_dev ? (long long)(*n_dev) : n_host;
+    if (n > capacity) n = capacity;
+
+    s_global_excl[t] = block_excl_scan_256(hist[t], s_tmp, nullptr);
+
+    while (true) {
+        if (t == 0) s_tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const long long tile = s_tile;  // super-tile index
+        const long long super_base = tile * (long long)(S * TILE);
+        if (super_base >= n) break;
+        status_next[tile * 256 + t] = 0;
+        uint32_t cnt[S], dst[S];  // digit t of sub-tile s: valid count, start inside the sorted sub-tile
+        int n_valid[S];
+#pragma unroll
+        for (int sub = 0; sub < S; ++sub) {
+            const long long tile_base = super_base + (long long)sub * TILE;
+            n_valid[sub] = (int)((n - tile_base < TILE) ? ((n - tile_base > 0) ? (n - tile_base) : 0) : TILE);
+            cnt[sub] = 0; dst[sub] = 0;
+            if (n_valid[sub] == 0) continue;  // block-uniform
+#pragma unroll
+            for (int w = 0; w < RS_WARPS; ++w) s_whist[w][t] = 0;
+            __syncthreads();
+            // ---- load (warp-striped: item i of lane l is element warp_base + i*32 + l)
+            uint32_t key[ITEMS], val[ITEMS];
+            const long long warp_base = tile_base + (long long)warp * (32 * ITEMS);
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i) {
+                const long long idx = warp_base + i * 32 + lane;
+                const bool valid = idx < n;
+                key[i] = valid ? keys_in[idx] : 0xFFFFFFFFu;
+                if (IDENTITY_VALS) val[i] = (uint32_t)idx;
+                else val[i] = valid ? vals_in[idx] : 0u;
+            }
+            // ---- rank inside the warp, digit counters per warp
+            uint32_t rank[ITEMS];
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i) {
+                const uint32_t d = (key[i] >> shift) & mask;
+                const uint32_t peers = match_digit(d, bits);
+                const int leader = __ffs(peers) - 1;
+                uint32_t old = 0;
+                if (lane == leader) {
+                    old = s_whist[warp][d];
+                    s_whist[warp][d] = (uint16_t)(old + __popc(peers));
+                }
+                old = __shfl_sync(0xffffffffu, old, leader);
+                rank[i] = old + __popc(peers & lt_mask);
+                __syncwarp();
+            }
+            __syncthreads();
+            // ---- per digit (thread t owns digit t): exclusive scan over warps, sub-tile count
+            uint32_t count = 0;
+#pragma unroll
+            for (int w = 0; w < RS_WARPS; ++w) {
+                const uint32_t c = s_whist[w][t];
+                s_whist[w][t] = (uint16_t)count;
+                count += c;
+            }
+            // padding keys (all ones) sit in digit `mask`, after every valid key of that digit
+            cnt[sub] = count - (((uint32_t)t == mask) ? (uint32_t)(TILE - n_valid[sub]) : 0u);
+            const uint32_t dstart = block_excl_scan_256(count, s_tmp, nullptr);
+            dst[sub] = dstart;
+            s_digit_start[t] = dstart;
+            __syncthreads();
+            // ---- park the sub-tile in shared memory in tile-sorted order
+            uint32_t* sk = s_keys + sub * TILE;
+            uint32_t* sv = s_vals + sub * TILE;
+#pragma unroll
+            for (int i = 0; i < ITEMS; ++i) {
+                const uint32_t d = (key[i] >> shift) & mask;
+                const uint32_t pos = s_digit_start[d] + s_whist[warp][d] + rank[i];
+                sk[pos] = key[i];
+                sv[pos] = val[i];
+            }
+            __syncthreads();  // s_whist / s_digit_start are rewritten by the next sub-tile
+        }
+        // ---- one count row and one look-back for the whole super-tile
+        uint32_t total = 0;
+#pragma unroll
+        for (int sub = 0; sub < S; ++sub) total += cnt[sub];
+        uint32_t prefix = 0;
+        if ((uint32_t)t <= mask) {  // digits above the mask do not exist in this pass
+            if (tile == 0) st_volatile_u32(&status_cur[t], RS_FLAG_INC | total);
+            else {
+                st_volatile_u32(&status_cur[tile * 256 + t], RS_FLAG_AGG | total);
+                prefix = look_back(status_cur, tile, t);
+                st_volatile_u32(&status_cur[tile * 256 + t], RS_FLAG_INC | (prefix + total));
+            }
+        }
+        uint32_t run = s_global_excl[t] + prefix;
+#pragma unroll
+        for (int sub = 0; sub < S; ++sub) {
+            s_bin_base[sub][t] = run - dst[sub];
+            run += cnt[sub];
+        }
+        __syncthreads();
+        // ---- contiguous runs per digit go out to global memory
+#pragma unroll
+        for (int sub = 0; sub < S; ++sub) {
+            const uint32_t* sk = s_keys + sub * TILE;
+            const uint32_t* sv = s_vals + sub * TILE;
+            for (int s = t; s < n_valid[sub]; s += RS_THREADS) {
+                const uint32_t k = sk[s];
+                const uint32_t d = (k >> shift) & mask;
+                const uint32_t o = s_bin_base[sub][d] + (uint32_t)s;
+                if (keys_out) keys_out[o] = k;
+                vals_out[o] = sv[s];
+            }
+        }
+        __syncthreads();  // staging and s_bin_base are rewritten by the next super-tile
+    }
+}
+
 int g_num_sms = 0;
 int num_sms() {
     if (g_num_sms == 0) {
@@ -279,6 +464,7 @@ int num_sms() {
 }  // namespace
 
 void set_sort_small_tiles(int v) { g_rs_small = v ? 1 : 0; }
+void set_sort_prefetch(int v) { g_rs_prefetch = v ? 1 : 0; }
 
 size_t sort_scratch_bytes(long long max_items, int key_bytes) {
     const int items = (key_bytes == 8) ? RsCfg<uint64_t>::SMALL : RsCfg<uint32_t>::SMALL;
@@ -308,6 +494,29 @@ void launch_pass(bool identity, unsigned grid, cudaStream_t stream, const KeyT* 
     else
         k_rs_pass<KeyT, ITEMS, false><<<grid, RS_THREADS, 0, stream>>>(kin, kout, vin, vout, n_host, n_dev, capacity, shift,
                                                                       bits, hist, ticket, st_cur, st_next);
+}
+
+// super-tile variant (32-bit keys): dynamic shared memory = S staged sub-tiles of keys + values
+constexpr int RS2_ITEMS = 16, RS2_S = 2;
+constexpr size_t RS2_SMEM = (size_t)RS2_S * RS_THREADS * RS2_ITEMS * (sizeof(uint32_t) + sizeof(uint32_t));
+int rs2_ctas_per_sm() {  // 0 = the variant cannot run here
+    static int n = -1;
+    if (n < 0) {
+        n = 0;
+        bool ok = true;
+        auto prep = [&](const void* f) {
+            ok = ok && cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS2_SMEM) == cudaSuccess;
+            ok = ok && cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess;
+        };
+        prep((const void*)k_rs_pass2<RS2_ITEMS, RS2_S, true>);
+        prep((const void*)k_rs_pass2<RS2_ITEMS, RS2_S, false>);
+        int nb = 0;
+        if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rs_pass2<RS2_ITEMS, RS2_S, false>, RS_THREADS,
+                                                                RS2_SMEM) == cudaSuccess)
+            n = nb;
+        cudaGetLastError();
+    }
+    return n;
 }
 
 template <typename KeyT>
@@ -348,8 +557,12 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
                                                                scratch->status[0], TILE);
         if (launch_count) ++*launch_count;
     }
-    const int per_sm = small ? 5 : 3;  // resident CTAs per SM (registers): persistent CTAs, one wave
-    long long grid = tiles_upper < (long long)sms * per_sm ? tiles_upper : (long long)sms * per_sm;
+    // super-tile variant: 32-bit keys, default tile size
+    int pf_ctas = 0;
+    if (sizeof(KeyT) == 4 && !small && g_rs_prefetch) pf_ctas = rs2_ctas_per_sm();
+    const int per_sm = pf_ctas > 0 ? pf_ctas : (small ? 5 : 3);  // resident CTAs per SM: persistent CTAs, one wave
+    const long long work_tiles = pf_ctas > 0 ? (tiles_upper + RS2_S - 1) / RS2_S : tiles_upper;
+    long long grid = work_tiles < (long long)sms * per_sm ? work_tiles : (long long)sms * per_sm;
     if (grid < 1) grid = 1;
     const KeyT* kin = keys_first; KeyT* kout = keys_tmp; KeyT* kother = keys;
     uint32_t* vin = vals; uint32_t* vout = vals_tmp;
@@ -358,7 +571,18 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
         uint32_t* st_cur = scratch->status[p & 1];
         uint32_t* st_next = scratch->status[(p + 1) & 1];
         const bool identity = (p == 0 && vals_identity);
-        if (small)
+        if (pf_ctas > 0) {
+            if constexpr (sizeof(KeyT) == 4) {
+                if (identity)
+                    k_rs_pass2<RS2_ITEMS, RS2_S, true><<<(unsigned)grid, RS_THREADS, RS2_SMEM, stream>>>(
+                        kin, kout, nullptr, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
+                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next);
+                else
+                    k_rs_pass2<RS2_ITEMS, RS2_S, false><<<(unsigned)grid, RS_THREADS, RS2_SMEM, stream>>>(
+                        kin, kout, vin, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
+                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next);
+            }
+        } else if (small)
             launch_pass<KeyT, RsCfg<KeyT>::SMALL>(identity, (unsigned)grid, stream, kin, kout, vin, vout, n_host, n_dev, capacity,
                                                   passes.shift[p], passes.bits[p], scratch->hist + p * 256,
                                                   scratch->tickets + p, st_cur, st_next);

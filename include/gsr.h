@@ -150,6 +150,7 @@ int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* c
 #define GSR_TUNE_BLEND_PPT 0
 #define GSR_TUNE_SORT_SMALL_TILES 1
 #define GSR_TUNE_BLEND_SHAPE8 2 /* 1 = a warp owns an 8-column block instead of 16 columns (main mode only) */
+#define GSR_TUNE_SORT_PREFETCH 4 /* 1 = radix passes prefetch the next tile with cp.async (32-bit keys) */
 #define GSR_TUNE_BLEND_SKIP 3   /* 1 = warp-level skip of quads that miss all of the warp's live pixels */
 int gsr_tune(gsr_t* h, int key, int value);
 

@@ -27,8 +27,5 @@ def run(tag):
 
 run("default")
 T = _gsr
-for ppt in (2, 4, 1):
-    for shape in (0, 1):
-        for skip in (0, 1):
-            r.tune(T.GSR_TUNE_BLEND_PPT, ppt); r.tune(T.GSR_TUNE_BLEND_SHAPE8, shape); r.tune(T.GSR_TUNE_BLEND_SKIP, skip)
-            run(f"ppt={ppt} shape8={shape} skip={skip}")
+for pf in (0, 1, 0, 1):
+    r.tune(T.GSR_TUNE_SORT_PREFETCH, pf); run(f"sort_prefetch={pf}")
