@@ -54,6 +54,8 @@ SIGNATURES = {
     "gsr_render_host": (C.c_int, [_vp, _vp, _vp]),
     "gsr_render_rgb8_host": (C.c_int, [_vp, _vp, _vp]),
     "gsr_render_r32f_host": (C.c_int, [_vp, _vp, _vp]),
+    "gsr_render_rgb8_host_async": (C.c_int, [_vp, _vp, _vp]),
+    "gsr_host_sync": (C.c_int, [_vp]),
     "gsr_render_batch": (C.c_int, [_vp, _fp, _fp, C.c_int, _vp, _vp]),
     "gsr_sort_depth": (C.c_int, [_vp, _fp, _vp, C.c_int, _vp]),
     "gsr_sort_pairs": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int, _vp]),

@@ -9,7 +9,9 @@
 //     output slot s * 32 + l of the warp's current 32 Gaussians and finds the owning Gaussian with a
 //     5-step binary search over the lanes' offsets (shuffles); the tile index comes from a multiply-high
 //     with a per-Gaussian magic reciprocal (no division); stores are contiguous.  Rectangles above
-//     DUP_BIG tiles are deferred and written by the whole CTA.
+//     DUP_BIG tiles go to a global list that k_duplicate_big spreads over the whole grid: the depth sort
+//     puts the Gaussians nearest to the camera - the ones with screen-sized rectangles - next to each
+//     other, so expanding them inside their own chunk left one CTA with most of the frame's instances.
 // Counterpart of the scan + duplicateWithKeys + identifyTileRanges steps of the tile rasteriser the
 // reference's CUDA backend calls (/root/reference/renderer_cuda.py:211-224); the OpenGL backend has no
 // tiles (its draw is one instanced quad per Gaussian, renderer_ogl.py:175-179).
@@ -21,7 +23,7 @@ constexpr int DUP_THREADS = 256;
 constexpr int DUP_WARPS = DUP_THREADS / 32;
 constexpr int DUP_ITEMS = 4;
 constexpr int DUP_CHUNK = DUP_THREADS * DUP_ITEMS;
-constexpr uint32_t DUP_BIG = 2048;  // instances; larger rectangles are expanded by the whole CTA
+constexpr uint32_t DUP_BIG = 256;    // instances; larger rectangles are expanded by k_duplicate_big
 constexpr unsigned long long CH_FLAG_AGG = 1ull << 62;
 constexpr unsigned long long CH_FLAG_INC = 2ull << 62;
 constexpr unsigned long long CH_FLAG_MASK = 3ull << 62;
@@ -53,12 +55,11 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
                                                           unsigned long long* __restrict__ chain,
                                                           uint32_t* __restrict__ ticket, void* __restrict__ out_keys,
                                                           uint32_t* __restrict__ out_gid, unsigned n,
-                                                          unsigned long long capacity) {
+                                                          unsigned long long capacity, uint4* __restrict__ big_list,
+                                                          uint32_t* __restrict__ big_count) {
     __shared__ uint32_t s_warp[DUP_WARPS + 1];
     __shared__ uint32_t s_chunk;
     __shared__ unsigned long long s_prefix;
-    __shared__ uint32_t s_nbig;
-    __shared__ uint32_t s_big[DUP_CHUNK][4];  // off, rx, ry, gid of deferred rectangles
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t tiles_x = (uint32_t)fp->tiles_x;
     const unsigned n_chunks = (n + DUP_CHUNK - 1) / DUP_CHUNK;
@@ -75,7 +76,7 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
     };
 
     while (true) {
-        if (t == 0) { s_chunk = atomicAdd(ticket, 1u); s_nbig = 0; }
+        if (t == 0) s_chunk = atomicAdd(ticket, 1u);
         __syncthreads();
         const unsigned chunk = s_chunk;
         if (chunk >= n_chunks) break;
@@ -140,20 +141,25 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
             }
             s_prefix = prefix;  // D and the overflow flag come from k_tile_scan
         }
-        // per-Gaussian reciprocal (owner lane), defer the huge ones
+        // per-Gaussian reciprocal (owner lane)
         uint32_t magic[DUP_ITEMS];
 #pragma unroll
         for (int i = 0; i < DUP_ITEMS; ++i) {
             magic[i] = magic_of(rx[i] >> 16);
             off[i] += wexcl;
-            if (cnt[i] > DUP_BIG) {
-                const uint32_t b = atomicAdd(&s_nbig, 1u);
-                s_big[b][0] = off[i]; s_big[b][1] = rx[i]; s_big[b][2] = ry[i]; s_big[b][3] = gid[i];
-                cnt[i] = 0;
-            }
         }
         __syncthreads();
         const unsigned long long prefix = s_prefix;
+        // large rectangles: (first output slot, rectangle, Gaussian) to the global list
+#pragma unroll
+        for (int i = 0; i < DUP_ITEMS; ++i) {
+            if (cnt[i] > DUP_BIG) {
+                const unsigned long long dst = prefix + off[i];
+                const uint32_t b = atomicAdd(big_count, 1u);
+                big_list[b] = make_uint4(dst > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)dst, rx[i], ry[i], gid[i]);
+                cnt[i] = 0;
+            }
+        }
         // ---- warp-cooperative emission, load balanced over INSTANCES: in each round the 32 Gaussians of the
         // warp (one per lane) own consecutive runs of the round's output; lane l of step s writes output
         // s * 32 + l and finds its owner by a 5-step binary search over the lanes' offsets (shuffles), so all
@@ -193,20 +199,43 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
                 }
             }
         }
-        // ---- deferred rectangles: whole CTA
-        const uint32_t nbig = s_nbig;
-        for (uint32_t b = 0; b < nbig; ++b) {
-            const uint32_t o = s_big[b][0], x = s_big[b][1], y = s_big[b][2], g = s_big[b][3];
-            const uint32_t w = x >> 16, c = w * (y >> 16);
-            const uint32_t tile0 = (y & 0xFFFFu) * tiles_x + (x & 0xFFFFu);
-            const uint32_t m = magic_of(w);
-            const bool small = c <= 65536u;
-            for (uint32_t k = t; k < c; k += DUP_THREADS) {
-                const uint32_t row = div_magic(k, w, m, small);
-                emit(prefix + o + k, tile0 + row * tiles_x + (k - row * w), g);
+        __syncthreads();
+    }
+}
+
+// Expands the large rectangles k_duplicate put on the global list: one warp per entry, entries dealt
+// round-robin to all warps of the grid (an entry is at most one screen of tiles).
+template <bool KEYS64>
+__global__ void __launch_bounds__(DUP_THREADS) k_duplicate_big(const FrameParams* __restrict__ fp, SplatBuffers sp,
+                                                              const uint4* __restrict__ big_list,
+                                                              const uint32_t* __restrict__ big_count,
+                                                              void* __restrict__ out_keys, uint32_t* __restrict__ out_gid,
+                                                              unsigned long long capacity) {
+    const uint32_t nb = *big_count;
+    const uint32_t tiles_x = (uint32_t)fp->tiles_x;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t n_warps = gridDim.x * (DUP_THREADS / 32);
+    // consecutive entries to different CTAs: neighbours on the list are neighbours in depth and similar in size
+    for (uint32_t b = blockIdx.x + gridDim.x * (threadIdx.x >> 5); b < nb; b += n_warps) {
+        const uint4 e = __ldg(big_list + b);
+        const uint32_t w = e.y >> 16, c = w * (e.z >> 16);
+        const uint32_t tile0 = (e.z & 0xFFFFu) * tiles_x + (e.y & 0xFFFFu);
+        const uint32_t m = magic_of(w);
+        const bool small = c <= 65536u;
+        uint32_t dk = 0;
+        if (KEYS64) dk = __ldg(sp.depth_key + e.w);
+        for (uint32_t k = lane; k < c; k += 32) {
+            const uint32_t row = div_magic(k, w, m, small);
+            const uint32_t tile = tile0 + row * tiles_x + (k - row * w);
+            const unsigned long long dst = (unsigned long long)e.x + k;
+            if (dst < capacity) {
+                if (KEYS64)
+                    reinterpret_cast<unsigned long long*>(out_keys)[dst] = ((unsigned long long)tile << 32) | dk;
+                else
+                    reinterpret_cast<uint32_t*>(out_keys)[dst] = tile;
+                out_gid[dst] = e.w;
             }
         }
-        __syncthreads();
     }
 }
 
@@ -361,26 +390,30 @@ int sm_count() {
 
 void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, SplatBuffers sp, FrameCounters* counters,
                              uint32_t* chain_status, uint32_t* chain_ticket, uint32_t* out_tile, uint32_t* out_gid,
-                             uint32_t* /*tile_hist*/, long long n, long long capacity, cudaStream_t s) {
+                             uint4* big_list, uint32_t* big_count, long long n, long long capacity, cudaStream_t s) {
     if (n <= 0) return;
     const long long chunks = (n + DUP_CHUNK - 1) / DUP_CHUNK;
     long long grid = chunks < (long long)sm_count() * 6 ? chunks : (long long)sm_count() * 6;
     k_duplicate<false><<<(unsigned)grid, DUP_THREADS, 0, s>>>(fp, sorted_gid, sp, counters,
                                                              reinterpret_cast<unsigned long long*>(chain_status),
                                                              chain_ticket, out_tile, out_gid, (unsigned)n,
-                                                             (unsigned long long)capacity);
+                                                             (unsigned long long)capacity, big_list, big_count);
+    k_duplicate_big<false><<<sm_count() * 4, DUP_THREADS, 0, s>>>(fp, sp, big_list, big_count, out_tile, out_gid,
+                                                                 (unsigned long long)capacity);
 }
 
 void launch_duplicate_keys64(const FrameParams* fp, SplatBuffers sp, FrameCounters* counters, uint32_t* chain_status,
-                             uint32_t* chain_ticket, uint64_t* out_keys, uint32_t* out_gid, long long n,
-                             long long capacity, cudaStream_t s) {
+                             uint32_t* chain_ticket, uint64_t* out_keys, uint32_t* out_gid, uint4* big_list,
+                             uint32_t* big_count, long long n, long long capacity, cudaStream_t s) {
     if (n <= 0) return;
     const long long chunks = (n + DUP_CHUNK - 1) / DUP_CHUNK;
     long long grid = chunks < (long long)sm_count() * 6 ? chunks : (long long)sm_count() * 6;
     k_duplicate<true><<<(unsigned)grid, DUP_THREADS, 0, s>>>(fp, nullptr, sp, counters,
                                                             reinterpret_cast<unsigned long long*>(chain_status),
                                                             chain_ticket, out_keys, out_gid, (unsigned)n,
-                                                            (unsigned long long)capacity);
+                                                            (unsigned long long)capacity, big_list, big_count);
+    k_duplicate_big<true><<<sm_count() * 4, DUP_THREADS, 0, s>>>(fp, sp, big_list, big_count, out_keys, out_gid,
+                                                                (unsigned long long)capacity);
 }
 
 template <typename KeyT>

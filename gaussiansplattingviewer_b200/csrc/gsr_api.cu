@@ -56,7 +56,8 @@ struct gsr_renderer {
     uint32_t* d_gid[2] = {nullptr, nullptr};   // depth-sort value ping-pong
     void* d_sortn = nullptr;                   // sort scratch sized for N
     SortScratch ss_n = {};
-    unsigned long long* d_chain = nullptr;     // duplicate: look-back words per chunk + ticket
+    unsigned long long* d_chain = nullptr;     // duplicate: look-back words per chunk + ticket + big-list counter
+    uint4* d_big = nullptr;                    // duplicate: large rectangles (N entries)
     size_t chain_bytes = 0;
     // per-instance buffers
     long long capacity = 0, capacity_req = 0;
@@ -73,6 +74,12 @@ struct gsr_renderer {
     int grid_w = 0;
     float* d_frame = nullptr;
     uint8_t* d_rgb8 = nullptr;
+    // pipelined read-back: second RGB8 buffer, copy stream, per-slot events
+    uint8_t* d_rgb8b = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_packed[2] = {}, ev_copied[2] = {};
+    bool slot_busy[2] = {false, false};
+    unsigned async_idx = 0;
     float* d_r32 = nullptr;
     // uniforms
     FrameParams fp = {};
@@ -100,7 +107,7 @@ int free_gaussian_buffers(gsr_t* h) {
     dfree(h->sp.rec0); dfree(h->sp.rec1); dfree(h->sp.rec2); dfree(h->sp.depth_key); dfree(h->sp.trect);
     dfree(h->sp.dbg_vsout); dfree(h->sp.dbg_setup);
     dfree(h->d_dkey[0]); dfree(h->d_dkey[1]); dfree(h->d_gid[0]); dfree(h->d_gid[1]);
-    dfree(h->d_sortn); dfree(h->d_chain);
+    dfree(h->d_sortn); dfree(h->d_chain); dfree(h->d_big);
     h->N = 0;
     return 0;
 }
@@ -130,8 +137,9 @@ int alloc_gaussian_buffers(gsr_t* h, long long n, int sh_dim) {
     }
     CK(cudaMalloc(&h->d_sortn, sort_scratch_bytes((long long)n1, 4)));
     sort_scratch_carve(&h->ss_n, h->d_sortn, (long long)n1, 4);
-    h->chain_bytes = ((n1 + 1023) / 1024 + 2) * 8;
+    h->chain_bytes = ((n1 + 1023) / 1024 + 3) * 8;
     CK(cudaMalloc(&h->d_chain, h->chain_bytes));
+    CK(cudaMalloc(&h->d_big, n1 * sizeof(uint4)));
     h->N = n;
     h->sh_dim = sh_dim;
     h->frame_valid = false;
@@ -213,12 +221,15 @@ int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bo
     if (timed) cudaEventRecord(h->ev[1], s);
     CK(cudaMemsetAsync(h->d_chain, 0, h->chain_bytes, s));
     uint32_t* chain_ticket = reinterpret_cast<uint32_t*>(h->d_chain + (h->chain_bytes / 8 - 1));
+    uint32_t* big_count = reinterpret_cast<uint32_t*>(h->d_chain + (h->chain_bytes / 8 - 2));
     const uint32_t* n_sort = &h->d_counters->n_sort;
     int res = 0;
     if (!keys64) {
         // depth sort of the N Gaussians (culled ones carry key 0xFFFFFFFF and sort to the end)
+        // (the two mantissa bytes of a depth key are spread over their bins, the exponent bytes are not)
+        SortOptions so_n = {0, false, false, 0x3u};
         const int r0 = radix_sort_pairs<uint32_t>(h->sp.depth_key, h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1],
-                                                  true, N, nullptr, N, 0, 32, &h->ss_n, s, &h->launches);
+                                                  true, N, nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
         const uint32_t* sorted_gid = h->d_gid[r0];
         if (timed) cudaEventRecord(h->ev[2], s);
         // counts -> ranges, D, overflow flag, digit histograms of the tile sort
@@ -227,10 +238,10 @@ int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bo
         h->launches += 1;
         if (timed) cudaEventRecord(h->ev[3], s);
         launch_duplicate_sorted(h->d_fp, sorted_gid, sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain),
-                                chain_ticket, (uint32_t*)h->d_ikeys[0], h->d_ivals[0], nullptr, N, cap, s);
-        h->launches += 1;
+                                chain_ticket, (uint32_t*)h->d_ikeys[0], h->d_ivals[0], h->d_big, big_count, N, cap, s);
+        h->launches += 2;
         if (timed) cudaEventRecord(h->ev[4], s);
-        SortOptions so = {scan_hist ? bits0 : 0, scan_hist, true};
+        SortOptions so = {scan_hist ? bits0 : 0, scan_hist, true, 0u};
         res = radix_sort_pairs<uint32_t>((uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[1],
                                          h->d_ivals[0], h->d_ivals[1], false, 0, n_sort, cap, 0, tbits, &h->ss_i, s,
                                          &h->launches, &so);
@@ -241,8 +252,8 @@ int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bo
         h->launches += 1;
         if (timed) cudaEventRecord(h->ev[3], s);
         launch_duplicate_keys64(h->d_fp, sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain), chain_ticket,
-                                (uint64_t*)h->d_ikeys[0], h->d_ivals[0], N, cap, s);
-        h->launches += 1;
+                                (uint64_t*)h->d_ikeys[0], h->d_ivals[0], h->d_big, big_count, N, cap, s);
+        h->launches += 2;
         if (timed) cudaEventRecord(h->ev[4], s);
         res = radix_sort_pairs<uint64_t>((uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[0], (uint64_t*)h->d_ikeys[1],
                                          h->d_ivals[0], h->d_ivals[1], false, 0, n_sort, cap, 0, 32 + tbits, &h->ss_i, s,
@@ -316,6 +327,11 @@ int gsr_create(int device, gsr_t** out) {
     CK(cudaMallocHost(&h->h_counters, sizeof(FrameCounters)));
     memset(h->h_counters, 0, sizeof(FrameCounters));
     for (auto& ev : h->ev) CK(cudaEventCreate(&ev));
+    CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+        CK(cudaEventCreateWithFlags(&h->ev_packed[i], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming));
+    }
     h->fp.scale_modifier = 1.f;
     h->fp.render_mod = 3;
     h->fp.flags = GSR_FLAG_CLAMP_UNORM;
@@ -329,7 +345,9 @@ int gsr_destroy(gsr_t* h) {
     cudaDeviceSynchronize();
     free_gaussian_buffers(h);
     free_instance_buffers(h);
-    dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
+    dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_rgb8b); dfree(h->d_r32);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    for (int i = 0; i < 2; ++i) { if (h->ev_packed[i]) cudaEventDestroy(h->ev_packed[i]); if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]); }
     dfree(h->d_fp); dfree(h->d_counters); dfree(h->d_sortp);
     if (h->h_counters) cudaFreeHost(h->h_counters);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
@@ -395,7 +413,8 @@ int gsr_set_resolution(gsr_t* h, int width, int height) {
     CK(cudaSetDevice(h->device));
     if (width == h->W && height == h->H) return 0;
     CK(cudaDeviceSynchronize());
-    dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_r32);
+    dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_rgb8b); dfree(h->d_r32);
+    h->slot_busy[0] = h->slot_busy[1] = false;
     h->W = width; h->H = height;
     h->tiles_x = (width + GSR_TILE - 1) / GSR_TILE;
     h->tiles_y = (height + GSR_TILE - 1) / GSR_TILE;
@@ -405,6 +424,7 @@ int gsr_set_resolution(gsr_t* h, int width, int height) {
     CK(cudaMalloc(&h->d_tile_grid, sizeof(int) * (size_t)h->grid_w * (h->tiles_y + 1) * GSR_GRID_REPLICAS));
     CK(cudaMalloc(&h->d_frame, npx * 16));
     CK(cudaMalloc(&h->d_rgb8, npx * 3));
+    CK(cudaMalloc(&h->d_rgb8b, npx * 3));
     CK(cudaMalloc(&h->d_r32, npx * 4));
     h->fp.W = width; h->fp.H = height; h->fp.tiles_x = h->tiles_x; h->fp.tiles_y = h->tiles_y;
     h->frame_valid = false;
@@ -491,6 +511,55 @@ int gsr_render_r32f_host(gsr_t* h, float* out, void* stream) {
     return render_to_host(h, out, 2, (cudaStream_t)stream);
 }
 
+namespace {
+// waits for an in-flight read-back slot; reports (and repairs) an instance-buffer overflow seen since
+int finish_slot(gsr_t* h, int slot) {
+    if (!h->slot_busy[slot]) return 0;
+    CK(cudaEventSynchronize(h->ev_copied[slot]));
+    h->slot_busy[slot] = false;
+    if (h->h_counters->overflow) {
+        const long long d = h->h_counters->n_instances;
+        const long long want = std::max(h->capacity * 2, d + d / 8);
+        h->capacity_req = 0;
+        h->h_counters->overflow = 0;
+        int rc = ensure_capacity(h, want, h->cap_keys64);
+        if (rc) return rc;
+        return fail(GSR_EOVERFLOW, "a pipelined frame overflowed the tile-instance buffers (grown now): submit it again");
+    }
+    return 0;
+}
+}  // namespace
+
+int gsr_render_rgb8_host_async(gsr_t* h, uint8_t* out, void* stream) {
+    if (!h || !out) return fail(GSR_EINVAL, "null argument");
+    CK(cudaSetDevice(h->device));
+    h->fp.sh_dim = h->sh_dim;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int slot = (int)(h->async_idx++ & 1u);
+    int rc = finish_slot(h, slot);
+    if (rc) return rc;
+    rc = render_frame(h, h->fp, h->d_frame, s, false);
+    if (rc) return rc;
+    const long long npx = (long long)h->W * h->H;
+    uint8_t* dev = slot ? h->d_rgb8b : h->d_rgb8;
+    launch_pack_rgb8(h->d_frame, dev, npx, s);
+    h->launches += 1;
+    CK(cudaEventRecord(h->ev_packed[slot], s));
+    CK(cudaStreamWaitEvent(h->copy_stream, h->ev_packed[slot], 0));
+    CK(cudaMemcpyAsync(out, dev, (size_t)npx * 3, cudaMemcpyDeviceToHost, h->copy_stream));
+    CK(cudaEventRecord(h->ev_copied[slot], h->copy_stream));
+    h->slot_busy[slot] = true;
+    return 0;
+}
+
+int gsr_host_sync(gsr_t* h) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    CK(cudaSetDevice(h->device));
+    int rc0 = finish_slot(h, 0);
+    int rc1 = finish_slot(h, 1);
+    return rc0 ? rc0 : rc1;
+}
+
 int gsr_render_batch(gsr_t* h, const float* views, const float* campos, int n_views, float* out_rgba, void* stream) {
     if (!h || !views || !campos || n_views < 0) return fail(GSR_EINVAL, "bad argument");
     CK(cudaSetDevice(h->device));
@@ -517,8 +586,9 @@ int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_i
     if (N == 0) return 0;
     launch_depth_keys(h->d_xyz, view, h->d_dkey[0], N, s);
     h->launches += 1;
+    SortOptions so_n = {0, false, false, 0x3u};  // mantissa bytes counted directly, see render_frame
     const int r = radix_sort_pairs<uint32_t>(h->d_dkey[0], h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1], true, N,
-                                             nullptr, N, 0, 32, &h->ss_n, s, &h->launches);
+                                             nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
     CK(cudaMemcpyAsync(out_index, h->d_gid[r], (size_t)N * 4,
                        dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
     if (!dst_is_device) CK(cudaStreamSynchronize(s));

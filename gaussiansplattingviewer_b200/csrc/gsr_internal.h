@@ -75,11 +75,13 @@ void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key
 // without being overwritten.
 // opt (may be nullptr): first_bits = width of the first digit (0 = 8; later digits are 8 bits wide);
 // hist_ready = scratch->hist already holds the per-pass digit counts (k_tile_scan), skip the histogram
-// kernel; vals_only_last = the last pass does not write keys (the caller only needs the permuted values).
+// kernel; vals_only_last = the last pass does not write keys (the caller only needs the permuted values);
+// hist_direct_mask: see k_rs_hist.
 struct SortOptions {
     int first_bits;
     bool hist_ready;
     bool vals_only_last;
+    unsigned hist_direct_mask;  // passes whose digits are spread over their bins: count them without the warp match
 };
 template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
@@ -95,13 +97,14 @@ void launch_pack_scene(const float* rot, const float* scale, const float* opacit
 void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
                        long long n, int sh_dim, cudaStream_t s);
 void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s);
+// big_list: N uint4 entries, big_count: one zeroed counter (large rectangles, see binning.cu)
 void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, SplatBuffers sp,
                              FrameCounters* counters, uint32_t* chain_status, uint32_t* chain_ticket,
-                             uint32_t* out_tile, uint32_t* out_gid, uint32_t* tile_hist /* [2][256] or nullptr */,
-                             long long n, long long capacity, cudaStream_t s);
-void launch_duplicate_keys64(const FrameParams* fp, SplatBuffers sp, FrameCounters* counters, uint32_t* chain_status,
-                             uint32_t* chain_ticket, uint64_t* out_keys, uint32_t* out_gid, long long n,
+                             uint32_t* out_tile, uint32_t* out_gid, uint4* big_list, uint32_t* big_count, long long n,
                              long long capacity, cudaStream_t s);
+void launch_duplicate_keys64(const FrameParams* fp, SplatBuffers sp, FrameCounters* counters, uint32_t* chain_status,
+                             uint32_t* chain_ticket, uint64_t* out_keys, uint32_t* out_gid, uint4* big_list,
+                             uint32_t* big_count, long long n, long long capacity, cudaStream_t s);
 template <typename KeyT>
 void launch_tile_ranges(const KeyT* sorted_keys, int key_shift, const FrameCounters* counters, long long capacity,
                         int2* ranges, int n_tiles, cudaStream_t s);

@@ -37,6 +37,7 @@ int g_rs_prefetch = 1;
 
 struct RsPasses {
     int n;
+    unsigned direct_mask;  // passes whose digit is counted without the warp-level match (k_rs_hist)
     int shift[8];
     int bits[8];
 };
@@ -156,14 +157,27 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const KeyT* __restrict__
     constexpr int VEC = 4;
     const long long n_vec = (reinterpret_cast<uintptr_t>(keys) % (sizeof(KeyT) * VEC)) ? 0 : n / VEC;
     const int lane = threadIdx.x & 31;
+    // Two ways to count a digit.  Shared-memory atomics retire about one lane per cycle per SM, so a digit
+    // whose values repeat inside a warp (exponent bytes of depth keys, high tile bits) is first aggregated
+    // with a ballot match (32 ALU instructions, then one atomic per distinct value); a digit that is spread
+    // over its bins (mantissa bytes) gains nothing from the match and goes straight to the atomic.  The
+    // caller says which passes are which (passes.direct_mask); padding keys (all ones: culled Gaussians)
+    // are always aggregated.
     auto count_key = [&](KeyT k, bool valid) {
         const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+        const bool ones = valid && (k == (KeyT) ~(KeyT)0);
+        const uint32_t omask = __ballot_sync(0xffffffffu, ones);
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
             if (p < passes.n) {
                 const uint32_t d = (uint32_t)(k >> passes.shift[p]) & ((1u << passes.bits[p]) - 1u);
-                const uint32_t peers = match_digit(d, passes.bits[p]) & vmask;
-                if (valid && lane == (__ffs(peers) - 1)) atomicAdd(&s_hist[p * 256 + d], __popc(peers));
+                if ((passes.direct_mask >> p) & 1) {
+                    if (valid && !ones) atomicAdd(&s_hist[p * 256 + d], 1u);
+                    if (omask && lane == (__ffs(omask) - 1)) atomicAdd(&s_hist[p * 256 + d], __popc(omask));
+                } else {
+                    const uint32_t peers = match_digit(d, passes.bits[p]) & vmask;
+                    if (valid && lane == (__ffs(peers) - 1)) atomicAdd(&s_hist[p * 256 + d], __popc(peers));
+                }
             }
         }
     };
@@ -528,6 +542,7 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
     const bool vals_only_last = opt && opt->vals_only_last;
     RsPasses passes;
     passes.n = 0;
+    passes.direct_mask = opt ? opt->hist_direct_mask : 0u;
     for (int b = begin_bit; b < end_bit && passes.n < 8;) {
         const int want = (passes.n == 0) ? first_bits : 8;
         passes.shift[passes.n] = b;

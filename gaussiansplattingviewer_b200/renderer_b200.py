@@ -212,6 +212,20 @@ class B200Renderer(GaussianRenderBase):
         _gsr.check(self._lib.gsr_render_rgb8_host(self._h, C.c_void_p(buf.data_ptr()), self._stream()))
         return buf.numpy()
 
+    def read_pixels_rgb8_async(self):
+        """Pipelined capture loop (main.py:793-917 renders and reads back every pose): like read_pixels_rgb8,
+        but returns at once; the copy to the host overlaps the next frame.  Returns the (H, W, 3) uint8 pinned
+        buffer the frame WILL land in: it is complete after the next-but-one call or after sync_host()."""
+        self._push_state()
+        k = self._async_k = getattr(self, "_async_k", 0) ^ 1
+        buf = self._pinned_buf(("rgb8a", k), (self.h, self.w, 3), self._torch.uint8)
+        _gsr.check(self._lib.gsr_render_rgb8_host_async(self._h, C.c_void_p(buf.data_ptr()), self._stream()))
+        return buf.numpy()
+
+    def sync_host(self):
+        """Waits for every pipelined read-back."""
+        _gsr.check(self._lib.gsr_host_sync(self._h))
+
     def read_pixels_r32f(self):
         """draw + glReadPixels(GL_RED, GL_FLOAT) (main.py:870): (H, W) float32."""
         self._push_state()

@@ -106,6 +106,15 @@ int gsr_render_host(gsr_t* h, float* out_rgba_host, void* stream);
 int gsr_render_rgb8_host(gsr_t* h, uint8_t* out_rgb_host, void* stream);
 int gsr_render_r32f_host(gsr_t* h, float* out_r_host, void* stream);
 
+/* Pipelined read-back for capture loops (main.py:793-917 renders and reads back hundreds of poses): enqueues
+ * draw + RGB8 conversion + copy into out_rgb_host (pinned host memory, H*W*3 bytes) and returns.  The copy of
+ * frame k runs on a second stream out of a second device buffer, so it overlaps the rendering of frame k+1.
+ * Two frames may be in flight: the call first waits for the frame submitted two calls earlier.  A host
+ * buffer is complete after the next-but-one call or after gsr_host_sync.  If a frame overflowed the
+ * instance buffers the sync point grows them and returns GSR_EOVERFLOW: submit that frame again. */
+int gsr_render_rgb8_host_async(gsr_t* h, uint8_t* out_rgb_host, void* stream);
+int gsr_host_sync(gsr_t* h);
+
 /* The render_all.py workload (render_all.py:14-35, main.py:793-840): n_views poses over one scene.
  * views: n_views x 16 floats, campos: n_views x 3 floats (HOST).  out_rgba: DEVICE buffer of
  * n_views*H*W*4 floats, or NULL to render every view into an internal scratch frame (throughput runs).
