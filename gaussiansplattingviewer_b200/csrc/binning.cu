@@ -124,22 +124,33 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
         __syncthreads();
         const uint32_t chunk_total = s_warp[DUP_WARPS];
         const uint32_t wexcl = s_warp[warp];
-        // ---- chain the chunk total (thread 0)
-        if (t == 0) {
+        // ---- chain the chunk total: warp 0 probes 32 predecessors per round trip (a one-thread walk left the
+        // other 255 threads at the barrier for most of the kernel: ncu barrier stall 9 per issue)
+        if (warp == 0) {
             unsigned long long prefix = 0;
             if (chunk == 0) {
-                st_volatile_u64(&chain[0], CH_FLAG_INC | (unsigned long long)chunk_total);
+                if (lane == 0) st_volatile_u64(&chain[0], CH_FLAG_INC | (unsigned long long)chunk_total);
             } else {
-                st_volatile_u64(&chain[chunk], CH_FLAG_AGG | (unsigned long long)chunk_total);
-                for (long long p = (long long)chunk - 1;; --p) {
-                    unsigned long long w;
-                    do { w = ld_volatile_u64(&chain[p]); } while ((w & CH_FLAG_MASK) == 0ull);
-                    prefix += w & CH_VAL_MASK;
-                    if (w & CH_FLAG_INC) break;
+                if (lane == 0) st_volatile_u64(&chain[chunk], CH_FLAG_AGG | (unsigned long long)chunk_total);
+                long long p = (long long)chunk - 1;
+                while (true) {
+                    const unsigned long long wd = (p - lane >= 0) ? ld_volatile_u64(&chain[p - lane]) : CH_FLAG_INC;
+                    const unsigned rdy = __ballot_sync(0xffffffffu, (wd & CH_FLAG_MASK) != 0ull);
+                    const unsigned inc = __ballot_sync(0xffffffffu, (wd & CH_FLAG_INC) != 0ull);
+                    const int n_ready = (rdy == 0xffffffffu) ? 32 : (__ffs(~rdy) - 1);  // usable: a run from lane 0
+                    const unsigned inc_in = inc & ((n_ready == 32) ? 0xffffffffu : ((1u << n_ready) - 1u));
+                    const int upto = inc_in ? __ffs(inc_in) : n_ready;  // lanes to add (the INC lane included)
+                    unsigned long long v = (lane < upto) ? (wd & CH_VAL_MASK) : 0ull;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                    prefix += v;
+                    if (inc_in) break;
+                    p -= upto;
+                    if (upto == 0) __nanosleep(128);
                 }
-                st_volatile_u64(&chain[chunk], CH_FLAG_INC | (prefix + chunk_total));
+                if (lane == 0) st_volatile_u64(&chain[chunk], CH_FLAG_INC | (prefix + chunk_total));
             }
-            s_prefix = prefix;  // D and the overflow flag come from k_tile_scan
+            if (lane == 0) s_prefix = prefix;  // D and the overflow flag come from k_tile_scan
         }
         // per-Gaussian reciprocal (owner lane)
         uint32_t magic[DUP_ITEMS];
@@ -256,11 +267,23 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int T = TX * TY;
     int* w = use_smem ? s_dyn : grid;
-    for (int i = t; i < TY * gw; i += TS_THREADS) {  // sum the replicas
-        int v = 0;
+    // sum the replicas; 4 elements x 16 replicas = 64 independent loads in flight per thread (one element at
+    // a time made this loop a chain of L2 round trips: 8 us of the kernel's 21 at 1080p)
+    for (int i0 = t; i0 < TY * gw; i0 += 4 * TS_THREADS) {
+        int v[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int r = 0; r < GSR_GRID_REPLICAS; ++r) v += grid[(size_t)r * grid_stride + i];
-        w[i] = v;
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * TS_THREADS;
+            if (i < TY * gw) {
+#pragma unroll
+                for (int r = 0; r < GSR_GRID_REPLICAS; ++r) v[u] += __ldg(grid + (size_t)r * grid_stride + i);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + u * TS_THREADS;
+            if (i < TY * gw) w[i] = v[u];
+        }
     }
     if (t < 512) s_hist[t] = 0;
     __syncthreads();
@@ -324,18 +347,35 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
     const bool overflow = total > capacity;
     unsigned long long start = s_w64[warp] + incl - sum;
     {
-        const uint32_t mask0 = (1u << bits0) - 1u;
+        // ranges + the high-digit histogram: the ids of a thread are consecutive, so they share their high
+        // digit except across a 2^bits0 boundary -> accumulate in a register, one shared atomic per run
         int y = id0 / TX, x = id0 - y * TX;
+        uint32_t run_digit = 0xFFFFFFFFu, run_sum = 0;
         for (int id = id0; id < id1; ++id) {
             const unsigned c = (unsigned)w[y * gw + x];
             ranges[id] = (overflow || c == 0) ? make_int2(0, 0) : make_int2((int)start, (int)(start + c));  // empty: (0, 0)
-            if (c) {
-                atomicAdd(&s_hist[(uint32_t)id & mask0], c);
-                atomicAdd(&s_hist[256 + ((uint32_t)id >> bits0)], c);
+            const uint32_t hd = (uint32_t)id >> bits0;
+            if (hd != run_digit) {
+                if (run_sum) atomicAdd(&s_hist[256 + run_digit], run_sum);
+                run_digit = hd; run_sum = 0;
             }
+            run_sum += c;
             start += c;
             if (++x == TX) { x = 0; ++y; }
         }
+        if (run_sum) atomicAdd(&s_hist[256 + run_digit], run_sum);
+    }
+    {
+        // low-digit histogram: thread t sums the tiles id = d + 2^bits0 * (slice + n_slices * j) of its digit d
+        const int nd = 1 << bits0;
+        const int n_slices = TS_THREADS >> bits0;  // >= 4 (bits0 <= 8)
+        const int d = t & (nd - 1), slice = t >> bits0;
+        uint32_t acc = 0;
+        for (int id = d + nd * slice; id < T; id += nd * n_slices) {
+            const int y = id / TX, x = id - y * TX;
+            acc += (unsigned)w[y * gw + x];
+        }
+        if (acc) atomicAdd(&s_hist[d], acc);
     }
     __syncthreads();
     if (t < 512) hist[t] = s_hist[t];

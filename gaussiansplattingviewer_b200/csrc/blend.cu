@@ -23,6 +23,8 @@
 namespace {
 
 constexpr int BL_BATCH = 128;  // records per shared-memory batch
+struct TagTrue { static constexpr bool value = true; };
+struct TagFalse { static constexpr bool value = false; };
 
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
@@ -119,12 +121,22 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
         } else {
             cp_async_wait<0>();
         }
-        __syncthreads();
+        const int cnt = min(BL_BATCH, range.y - range.x - b * BL_BATCH);
+        // does the batch hold a splat whose conic is not safely positive definite (rec2.w, set by the preprocess
+        // kernel)?  Only then can the shader's `power > 0 -> discard` fire; every thread looks at the records it
+        // staged itself and the barrier ORs the answers, so the usual batch runs the loop without that test.
+        bool flagged = false;
+#pragma unroll
+        for (int i = 0; i < PER_THREAD; ++i) {
+            const int slot = threadIdx.x + i * THREADS;
+            if (slot < cnt) flagged = flagged || (s2[buf][slot].w != 0.f);
+        }
+        const bool check_power = __syncthreads_or(flagged ? 1 : 0) != 0;
         bool live = false;
 #pragma unroll
         for (int k = 0; k < PPT; ++k) live = live || (T[k] >= 1e-4f);
-        if (__any_sync(0xffffffffu, live)) {
-            const int cnt = min(BL_BATCH, range.y - range.x - b * BL_BATCH);
+        auto run_batch = [&](auto tag) {
+            constexpr bool CHECK_POWER = decltype(tag)::value;
 #pragma unroll 2
             for (int j = 0; j < cnt; ++j) {
                 const float4 a = s0[buf][j];  // cx, cy, hx, hy
@@ -143,7 +155,7 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                 // no live pixel of this warp lies inside the quad: skip the splat for 3 instructions
                 if (SKIP && !__any_sync(0xffffffffu, any_in)) continue;
                 const float4 q = s1[buf][j];  // A', B', C' (pre-scaled conic), opacity
-                const float4 c = s2[buf][j];  // r, g, b, depth
+                const float4 c = s2[buf][j];  // r, g, b, flag: conic not positive definite
                 const float bdx = q.y * dx;
                 const float adx2 = q.x * dx * dx;
 #pragma unroll
@@ -158,7 +170,8 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                         const float p2 = fmaf(fmaf(q.z, dy[k], bdx), dy[k], adx2);  // log2(e) * power
                         const float e = ex2_approx(p2);
                         const float alpha = fminf(0.99f, q.w * e);
-                        valid = valid && !(p2 > 0.f) && !(alpha < 1.f / 255.f);
+                        valid = valid && !(alpha < 1.f / 255.f);
+                        if (CHECK_POWER) valid = valid && !(p2 > 0.f);
                         if (MODE == 0) {
                             if (COUNT) n_hit += valid ? 1u : 0u;
                             const float w = valid ? alpha * T[k] : 0.f;
@@ -179,6 +192,10 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                     }
                 }
             }
+        };
+        if (__any_sync(0xffffffffu, live)) {
+            if (check_power) run_batch(TagTrue{});
+            else run_batch(TagFalse{});
         }
         bool live2 = false;
 #pragma unroll

@@ -32,7 +32,7 @@ struct FrameCounters {
 // Splat record, three float4 planes indexed by Gaussian:
 //   rec0 = (cx, cy, hx, hy)            splat centre (window coordinates) and 3-sigma half extents
 //   rec1 = (A', B', C', opacity)       conic pre-scaled: log2(e) * power = A' dx^2 + B' dx dy + C' dy^2
-//   rec2 = (r, g, b, depth)
+//   rec2 = (r, g, b, flag)             flag = 1: conic not safely positive definite (keep the power > 0 test)
 // plus the tile rectangle trect = (tx0 | tiles_wide << 16, ty0 | tiles_high << 16), 0 x 0 when culled.
 struct SceneBuffers {
     const float* xyz;      // N x 3

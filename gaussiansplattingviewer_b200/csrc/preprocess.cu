@@ -292,7 +292,12 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
             const float L2E = 1.4426950408889634f;
             out.rec0[g] = make_float4(cx, cy, hx, hy);
             out.rec1[g] = make_float4(conic0 * (-0.5f * L2E), conic1 * (-L2E), conic2 * (-0.5f * L2E), alpha);
-            out.rec2[g] = make_float4(c0, c1, c2, depth);
+            // rec2.w: 0 when the conic is positive definite with a margin, i.e. power <= 0 at every pixel even
+            // after rounding (A, C > 0 and det > 1e-5 A C: the cancellation error of the quadratic form is a few
+            // 1e-7 of its terms); 1 tells the blend kernel to keep the shader's `power > 0` discard for this splat
+            const bool pd = (conic0 > 0.f) && (conic2 > 0.f) &&
+                            ((conic0 * conic2 - conic1 * conic1) > 1e-5f * (conic0 * conic2));
+            out.rec2[g] = make_float4(c0, c1, c2, pd ? 0.f : 1.f);
         }
         out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
         out.trect[g] = trect;
