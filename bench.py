@@ -314,12 +314,25 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    # stdout carries exactly one JSON line: everything libraries print there (NCCL's version banner, ...) is
+    # sent to stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
+
     if args.impl == "reference":
         line = run_reference(args)
         if line is not None:
-            print(json.dumps(line))
+            emit(line)
         return
     o = run_ours(args)
+    if o["world"] > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
     if o["rank"] != 0:
         return
     K, world, W, H, n = o["K"], o["world"], o["W"], o["H"], o["n"]
@@ -378,7 +391,7 @@ def main():
                                 "kind": "port", "sample": "one full frame of the same workload (last timed pose): numpy "
                                 "depth sort %.2f s + oracle/gs_oracle.c rasteriser %.2f s" % (t_sort, t_rast),
                                 "max_abs_diff_vs_gpu": float(np.abs(gpu_img - img).max())}
-    print(json.dumps(line))
+    emit(line)
 
 
 if __name__ == "__main__":

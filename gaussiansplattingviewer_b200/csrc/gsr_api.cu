@@ -179,7 +179,10 @@ int ensure_capacity(gsr_t* h, long long want, bool keys64) {
 
 long long auto_capacity(const gsr_t* h) {
     if (h->capacity_req > 0) return h->capacity_req;
-    return std::min<long long>(std::max<long long>(4ll << 20, 16 * h->N), MAX_CAPACITY);
+    // instances per Gaussian grow with the pixel count: 16 per Gaussian up to 1080p, 4x that at 4K and above
+    const double px = (double)h->W * (double)h->H / (1920.0 * 1080.0);
+    const long long per = (long long)(16.0 * std::min(4.0, std::max(1.0, px)));
+    return std::min<long long>(std::max<long long>(4ll << 20, per * h->N), MAX_CAPACITY);
 }
 
 int tile_bits(int n_tiles) {

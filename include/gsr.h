@@ -87,7 +87,7 @@ int gsr_set_camera(gsr_t* h, const float view[16], const float proj[16], const f
  * -1 disparity ("depth", 1.2x scale), -2 billboard, -3 flat ball, -4 gaussian ball (gau_frag.glsl:7) */
 int gsr_set_params(gsr_t* h, float scale_modifier, int render_mod, unsigned flags);
 
-/* Instance capacity of the work buffers (0 = automatic: max(4M, 16 N), grown on overflow by the
+/* Instance capacity of the work buffers (0 = automatic: max(4M, 16 N), x pixels/1080p up to 4x, grown on overflow by the
  * *_host entry points). */
 int gsr_set_capacity(gsr_t* h, long long max_instances);
 
