@@ -34,6 +34,11 @@ class Stats(C.Structure):
     ]
 
 
+class PlyLayout(C.Structure):
+    # gsr_ply_layout: x y z | f_dc_0..2 | f_rest_0..44 | opacity | scale_0..2 | rot_0..3
+    _fields_ = [("row_bytes", C.c_int32), ("big_endian", C.c_int32), ("offset", C.c_int32 * 59)]
+
+
 _fp = C.POINTER(C.c_float)
 _vp = C.c_void_p
 _ll = C.c_longlong
@@ -45,6 +50,8 @@ SIGNATURES = {
     "gsr_last_error": (C.c_char_p, []),
     "gsr_version": (C.c_int, []),
     "gsr_set_gaussians": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int]),
+    "gsr_load_ply_rows": (C.c_int, [_vp, _vp, _ll, C.POINTER(PlyLayout), C.c_int, _fp, _fp, _vp]),
+    "gsr_get_gaussians": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "gsr_set_resolution": (C.c_int, [_vp, C.c_int, C.c_int]),
     "gsr_set_camera": (C.c_int, [_vp, _fp, _fp, _fp, C.c_float, C.c_float, C.c_float]),
     "gsr_set_params": (C.c_int, [_vp, C.c_float, C.c_int, C.c_uint]),
@@ -56,6 +63,7 @@ SIGNATURES = {
     "gsr_render_r32f_host": (C.c_int, [_vp, _vp, _vp]),
     "gsr_render_rgb8_host_async": (C.c_int, [_vp, _vp, _vp]),
     "gsr_host_sync": (C.c_int, [_vp]),
+    "gsr_capture_stereo_async": (C.c_int, [_vp, _fp, _fp, _fp, _fp, _vp, _vp, _vp, C.c_int, _vp]),
     "gsr_render_batch": (C.c_int, [_vp, _fp, _fp, C.c_int, _vp, _vp]),
     "gsr_sort_depth": (C.c_int, [_vp, _fp, _vp, C.c_int, _vp]),
     "gsr_sort_pairs": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int, _vp]),

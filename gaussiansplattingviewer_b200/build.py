@@ -23,6 +23,7 @@ SOURCES = {
     "binning.cu": [],
     "blend.cu": [],
     "instrument.cu": [],
+    "ply_decode.cu": ["-fmad=false"],
     "gsr_api.cu": ["-Xcompiler", "-fvisibility=default"],
 }
 

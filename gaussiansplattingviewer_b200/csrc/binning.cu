@@ -382,6 +382,10 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
     if (t == 0) {
         counters->n_instances = (total > 0xFFFFFFFFull) ? 0xFFFFFFFFu : (unsigned)total;
         counters->overflow = overflow ? 1u : 0u;
+        if (overflow) {
+            counters->sticky_overflow += 1u;
+            counters->sticky_max_d = max(counters->sticky_max_d, (unsigned)min(total, (unsigned long long)0xFFFFFFFFu));
+        }
         counters->n_sort = overflow ? 0u : (unsigned)total;
     }
     (void)s_wsum;

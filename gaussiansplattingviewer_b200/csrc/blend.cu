@@ -239,6 +239,17 @@ __global__ void k_extract_r(const float4* __restrict__ rgba, float* __restrict__
     if (i < n_px) r[i] = rgba[i].x;
 }
 
+// (disparity * 65535).astype(np.uint16) of main.py:878-879: float32 product, truncation toward zero, wrap
+// modulo 2^16 like the x86 conversion NumPy's cast compiles to (out of the int32 range, or NaN -> 0)
+__global__ void k_pack_disp_u16(const float4* __restrict__ rgba, uint16_t* __restrict__ d, long long n_px) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_px) return;
+    const float v = __fmul_rn(rgba[i].x, 65535.f);
+    int q = 0;
+    if (fabsf(v) < 2147483648.f) q = __float2int_rz(v);
+    d[i] = (uint16_t)(unsigned)q;
+}
+
 // kernel-variant knobs (gsr_tune): pixels per thread, warp block shape, warp-level quad skip
 int g_blend_ppt = 2, g_blend_shape8 = 1, g_blend_skip = 1;
 
@@ -296,6 +307,9 @@ void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_
 
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s) {
     k_pack_rgb8<<<(unsigned)((n_px + 255) / 256), 256, 0, s>>>(reinterpret_cast<const float4*>(rgba), rgb, n_px);
+}
+void launch_pack_disp_u16(const float* rgba, uint16_t* d, long long n_px, cudaStream_t s) {
+    k_pack_disp_u16<<<(unsigned)((n_px + 255) / 256), 256, 0, s>>>(reinterpret_cast<const float4*>(rgba), d, n_px);
 }
 void launch_extract_r(const float* rgba, float* r, long long n_px, cudaStream_t s) {
     k_extract_r<<<(unsigned)((n_px + 255) / 256), 256, 0, s>>>(reinterpret_cast<const float4*>(rgba), r, n_px);

@@ -76,6 +76,8 @@ struct gsr_renderer {
     uint8_t* d_rgb8 = nullptr;
     // pipelined read-back: second RGB8 buffer, copy stream, per-slot events
     uint8_t* d_rgb8b = nullptr;
+    uint8_t* d_cap[2] = {nullptr, nullptr};  // stereo capture slots: left RGB8 | right RGB8 | disparity u16
+    int order_buf = -1;                      // d_gid[] buffer holding a shared depth order (stereo capture)
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_packed[2] = {}, ev_copied[2] = {};
     bool slot_busy[2] = {false, false};
@@ -143,6 +145,7 @@ int alloc_gaussian_buffers(gsr_t* h, long long n, int sh_dim) {
     h->N = n;
     h->sh_dim = sh_dim;
     h->frame_valid = false;
+    h->order_buf = -1;
     return 0;
 }
 
@@ -192,7 +195,14 @@ int tile_bits(int n_tiles) {
 }
 
 // Enqueues one frame.  timed: record events between stages (h->ev[0..6]).
-int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bool timed) {
+// order_mode: 0 = sort this frame's depth keys; 1 = same, with keys for every Gaussian in front of the camera, and
+// remember the order; 2 = reuse the remembered order (same view-space depths: same view up to an in-plane shift)
+int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode = 0) {
+    FrameParams fp = fp_in;
+    if (fp.flags & GSR_FLAG_KEYS64) order_mode = 0;
+    if (order_mode == 2 && h->order_buf < 0) order_mode = 1;
+    fp.flags &= ~GSR_FLAG_INTERNAL_DEPTH_ALL;
+    if (order_mode == 1) fp.flags |= GSR_FLAG_INTERNAL_DEPTH_ALL;
     if (h->N <= 0 && !h->d_xyz) return fail(GSR_EINVAL, "no gaussians set");
     if (h->W <= 0) return fail(GSR_EINVAL, "no resolution set");
     if (!h->have_camera) return fail(GSR_EINVAL, "no camera set");
@@ -231,8 +241,12 @@ int render_frame(gsr_t* h, const FrameParams& fp, float* out, cudaStream_t s, bo
         // depth sort of the N Gaussians (culled ones carry key 0xFFFFFFFF and sort to the end)
         // (the two mantissa bytes of a depth key are spread over their bins, the exponent bytes are not)
         SortOptions so_n = {0, false, false, 0x3u};
-        const int r0 = radix_sort_pairs<uint32_t>(h->sp.depth_key, h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1],
-                                                  true, N, nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
+        int r0 = h->order_buf;
+        if (order_mode != 2) {
+            r0 = radix_sort_pairs<uint32_t>(h->sp.depth_key, h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1],
+                                            true, N, nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
+            h->order_buf = (order_mode == 1) ? r0 : -1;
+        }
         const uint32_t* sorted_gid = h->d_gid[r0];
         if (timed) cudaEventRecord(h->ev[2], s);
         // counts -> ranges, D, overflow flag, digit histograms of the tile sort
@@ -349,6 +363,7 @@ int gsr_destroy(gsr_t* h) {
     free_gaussian_buffers(h);
     free_instance_buffers(h);
     dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_rgb8b); dfree(h->d_r32);
+    dfree(h->d_cap[0]); dfree(h->d_cap[1]);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     for (int i = 0; i < 2; ++i) { if (h->ev_packed[i]) cudaEventDestroy(h->ev_packed[i]); if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]); }
     dfree(h->d_fp); dfree(h->d_counters); dfree(h->d_sortp);
@@ -398,6 +413,108 @@ int gsr_set_gaussians(gsr_t* h, const float* xyz, const float* rot, const float*
     return 0;
 }
 
+// load_ply on the device (util_gau.py:63-125): raw vertex rows -> resident scene planes, bbox, center.
+int gsr_load_ply_rows(gsr_t* h, const void* rows, long long n, const gsr_ply_layout* layout, int src_is_device,
+                      float bbox[6], float center[3], void* stream) {
+    if (!h || !layout || (n > 0 && !rows)) return fail(GSR_EINVAL, "null argument");
+    if (n < 0) return fail(GSR_EINVAL, "bad vertex count");
+    PlyLayout lay;
+    lay.row_bytes = layout->row_bytes;
+    lay.big_endian = layout->big_endian ? 1 : 0;
+    if (lay.row_bytes < 59 * 4 || lay.row_bytes % 4) return fail(GSR_EINVAL, "row_bytes must be a multiple of 4 and hold 59 floats");
+    for (int i = 0; i < 59; ++i) {
+        const int o = layout->offset[i];
+        if (o < 0 || o % 4 || o + 4 > lay.row_bytes) return fail(GSR_EINVAL, "bad property offset");
+        lay.off[i] = o;
+    }
+    if (ply_decode_configure(lay.row_bytes)) return fail(GSR_EINVAL, "vertex row too wide");
+    int rc = gsr_alloc_gaussians(h, n, 48);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, h->device);
+    int* d_red = nullptr;   // 7 ordered ints + 3 running sums | 6 bbox floats + 3 center floats
+    CK(cudaMalloc(&d_red, 20 * 4));
+    float* d_out = reinterpret_cast<float*>(d_red) + 10;
+    launch_ply_bbox_init(d_red, s);
+    h->launches += 1;
+    const size_t rb = (size_t)lay.row_bytes;
+    unsigned char* d_stage[2] = {nullptr, nullptr};
+    cudaEvent_t ev_up[2] = {}, ev_done[2] = {};
+    int ret = 0;
+    if (src_is_device) {
+        if (((uintptr_t)rows & 15) != 0) { cudaFree(d_red); return fail(GSR_EINVAL, "device rows must be 16-byte aligned"); }
+        launch_ply_decode((const unsigned char*)rows, lay, n, 0, h->d_xyz, h->d_rot, h->d_scale_op, h->d_sh, d_red, sm_count, s);
+        if (center) launch_ply_center(h->d_xyz, n, d_red, s);
+        h->launches += (n > 0) * (center ? 2 : 1);
+    } else if (n > 0) {
+        // double-buffered upload: chunk k+1 crosses PCIe on the copy stream while chunk k is decoded
+        const long long chunk_rows = std::max<long long>(128, ((64ll << 20) / (long long)rb) / 128 * 128);
+        const size_t stage_bytes = ((size_t)chunk_rows * rb + 15) & ~(size_t)15;
+        for (int i = 0; i < 2 && !ret; ++i) {
+            if (cudaMalloc(&d_stage[i], stage_bytes) != cudaSuccess) ret = GSR_ENOMEM;
+            else if (cudaEventCreateWithFlags(&ev_up[i], cudaEventDisableTiming) != cudaSuccess ||
+                     cudaEventCreateWithFlags(&ev_done[i], cudaEventDisableTiming) != cudaSuccess) ret = GSR_ECUDA;
+        }
+        int k = 0;
+        for (long long r0 = 0; r0 < n && !ret; r0 += chunk_rows, ++k) {
+            const int b = k & 1;
+            const long long nr = std::min(chunk_rows, n - r0);
+            if (k >= 2) cudaStreamWaitEvent(h->copy_stream, ev_done[b], 0);  // buffer b was decoded
+            if (cudaMemcpyAsync(d_stage[b], (const unsigned char*)rows + (size_t)r0 * rb, (size_t)nr * rb,
+                                cudaMemcpyHostToDevice, h->copy_stream) != cudaSuccess) { ret = GSR_ECUDA; break; }
+            cudaEventRecord(ev_up[b], h->copy_stream);
+            cudaStreamWaitEvent(s, ev_up[b], 0);
+            launch_ply_decode(d_stage[b], lay, nr, r0, h->d_xyz, h->d_rot, h->d_scale_op, h->d_sh, d_red, sm_count, s);
+            cudaEventRecord(ev_done[b], s);
+            // the serial running sum of this chunk hides behind the upload of the next one
+            if (center) launch_ply_center(h->d_xyz + r0 * 3, nr, d_red, s);
+            h->launches += center ? 2 : 1;
+        }
+    }
+    if (!ret) {
+        launch_ply_final(d_red, n, d_out, d_out + 6, s);
+        h->launches += 1;
+        float host[9] = {0};
+        if (cudaMemcpyAsync(host, d_out, sizeof(host), cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+            cudaStreamSynchronize(s) != cudaSuccess) ret = GSR_ECUDA;
+        else {
+            if (bbox) memcpy(bbox, host, 6 * sizeof(float));
+            if (center) {
+                memcpy(center, host + 6, 3 * sizeof(float));
+                if (n == 0) center[0] = center[1] = center[2] = nanf("");  // np.mean of an empty axis
+            }
+        }
+    }
+    cudaStreamSynchronize(h->copy_stream);
+    cudaError_t e = cudaGetLastError();
+    for (int i = 0; i < 2; ++i) {
+        if (d_stage[i]) cudaFree(d_stage[i]);
+        if (ev_up[i]) cudaEventDestroy(ev_up[i]);
+        if (ev_done[i]) cudaEventDestroy(ev_done[i]);
+    }
+    cudaFree(d_red);
+    if (ret == GSR_ENOMEM) return fail(GSR_ENOMEM, "staging buffers for the PLY upload");
+    if (ret || e != cudaSuccess) return fail(GSR_ECUDA, std::string("PLY decode: ") + cudaGetErrorString(e));
+    return 0;
+}
+
+// inverse of gsr_set_gaussians: resident planes -> GaussianData's five host arrays
+int gsr_get_gaussians(gsr_t* h, float* xyz, float* rot, float* scale, float* opacity, float* sh) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    if (!h->d_xyz) return fail(GSR_EINVAL, "no gaussians set");
+    const size_t n = (size_t)h->N;
+    if (n == 0) return 0;
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    if (xyz) CK(cudaMemcpy(xyz, h->d_xyz, n * 12, cudaMemcpyDeviceToHost));
+    if (rot) CK(cudaMemcpy(rot, h->d_rot, n * 16, cudaMemcpyDeviceToHost));
+    if (scale) CK(cudaMemcpy2D(scale, 12, h->d_scale_op, 16, 12, n, cudaMemcpyDeviceToHost));
+    if (opacity) CK(cudaMemcpy2D(opacity, 4, reinterpret_cast<const char*>(h->d_scale_op) + 12, 16, 4, n, cudaMemcpyDeviceToHost));
+    if (sh) CK(cudaMemcpy(sh, h->d_sh, n * (size_t)h->sh_dim * 4, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 int gsr_scene_buffer(gsr_t* h, int which, void** dev_ptr, long long* bytes) {
     if (!h || !dev_ptr || !bytes) return fail(GSR_EINVAL, "null argument");
     const long long n = h->N;
@@ -417,6 +534,7 @@ int gsr_set_resolution(gsr_t* h, int width, int height) {
     if (width == h->W && height == h->H) return 0;
     CK(cudaDeviceSynchronize());
     dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_rgb8b); dfree(h->d_r32);
+    dfree(h->d_cap[0]); dfree(h->d_cap[1]);
     h->slot_busy[0] = h->slot_busy[1] = false;
     h->W = width; h->H = height;
     h->tiles_x = (width + GSR_TILE - 1) / GSR_TILE;
@@ -520,14 +638,20 @@ int finish_slot(gsr_t* h, int slot) {
     if (!h->slot_busy[slot]) return 0;
     CK(cudaEventSynchronize(h->ev_copied[slot]));
     h->slot_busy[slot] = false;
-    if (h->h_counters->overflow) {
-        const long long d = h->h_counters->n_instances;
+    // the sticky words count every overflowed frame since the last clear, whichever frame the pinned copy is from
+    if (h->h_counters->sticky_overflow) {
+        const long long d = std::max<long long>(h->h_counters->sticky_max_d, h->h_counters->n_instances);
         const long long want = std::max(h->capacity * 2, d + d / 8);
         h->capacity_req = 0;
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemset(&h->d_counters->sticky_overflow, 0, 8));
+        h->h_counters->sticky_overflow = 0;
+        h->h_counters->sticky_max_d = 0;
         h->h_counters->overflow = 0;
+        h->slot_busy[0] = h->slot_busy[1] = false;
         int rc = ensure_capacity(h, want, h->cap_keys64);
         if (rc) return rc;
-        return fail(GSR_EOVERFLOW, "a pipelined frame overflowed the tile-instance buffers (grown now): submit it again");
+        return fail(GSR_EOVERFLOW, "a pipelined frame overflowed the tile-instance buffers (grown now): submit the frames in flight again");
     }
     return 0;
 }
@@ -550,6 +674,72 @@ int gsr_render_rgb8_host_async(gsr_t* h, uint8_t* out, void* stream) {
     CK(cudaEventRecord(h->ev_packed[slot], s));
     CK(cudaStreamWaitEvent(h->copy_stream, h->ev_packed[slot], 0));
     CK(cudaMemcpyAsync(out, dev, (size_t)npx * 3, cudaMemcpyDeviceToHost, h->copy_stream));
+    CK(cudaEventRecord(h->ev_copied[slot], h->copy_stream));
+    h->slot_busy[slot] = true;
+    return 0;
+}
+
+// One pose of the stereo capture loop (main.py:844-917): left RGB8, disparity u16 at the left pose, right RGB8.
+int gsr_capture_stereo_async(gsr_t* h, const float view_left[16], const float campos_left[3], const float view_right[16],
+                             const float campos_right[3], uint8_t* left_rgb, uint16_t* disparity, uint8_t* right_rgb,
+                             int share_order, void* stream) {
+    if (!h || !view_left || !campos_left) return fail(GSR_EINVAL, "null argument");
+    if (right_rgb && (!view_right || !campos_right)) return fail(GSR_EINVAL, "right image without a right pose");
+    CK(cudaSetDevice(h->device));
+    if (h->W <= 0) return fail(GSR_EINVAL, "no resolution set");
+    h->fp.sh_dim = h->sh_dim;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int slot = (int)(h->async_idx++ & 1u);
+    int rc = finish_slot(h, slot);
+    if (rc) return rc;
+    const size_t npx = (size_t)h->W * h->H;
+    if (!h->d_cap[slot]) CK(cudaMalloc(&h->d_cap[slot], npx * 8));
+    uint8_t* d_left = h->d_cap[slot];
+    uint8_t* d_right = d_left + npx * 3;
+    uint16_t* d_disp = reinterpret_cast<uint16_t*>(d_left + npx * 6);
+    // the three renders have the same view-space depth per Gaussian (same view; the right view differs by an
+    // x translation in view space, main.py:376-380), so one depth order serves all of them
+    int mode = share_order ? 1 : 0;
+    FrameParams fp = h->fp;
+    memcpy(fp.view, view_left, 64);
+    memcpy(fp.campos, campos_left, 12);
+    if (left_rgb) {
+        fp.flags |= GSR_FLAG_CLAMP_UNORM;  // RGB8 FBO (main.py:846-852)
+        rc = render_frame(h, fp, h->d_frame, s, false, mode);
+        if (rc) return rc;
+        if (mode) mode = 2;
+        launch_pack_rgb8(h->d_frame, d_left, (long long)npx, s);
+        h->launches += 1;
+    }
+    if (disparity) {
+        FrameParams fd = fp;
+        fd.render_mod = -1;                  // main.py:866
+        fd.flags &= ~GSR_FLAG_CLAMP_UNORM;   // R32F FBO (main.py:858-870)
+        rc = render_frame(h, fd, h->d_frame, s, false, mode);
+        if (rc) return rc;
+        if (mode) mode = 2;
+        launch_pack_disp_u16(h->d_frame, d_disp, (long long)npx, s);
+        h->launches += 1;
+    }
+    if (right_rgb) {
+        FrameParams fr = fp;
+        fr.flags |= GSR_FLAG_CLAMP_UNORM;
+        memcpy(fr.view, view_right, 64);
+        memcpy(fr.campos, campos_right, 12);
+        if (mode == 2) {  // the shared order needs equal depth rows; otherwise sort again
+            for (int k = 8; k < 12; ++k) if (fr.view[k] != fp.view[k]) mode = 0;
+        }
+        rc = render_frame(h, fr, h->d_frame, s, false, mode);
+        if (rc) return rc;
+        launch_pack_rgb8(h->d_frame, d_right, (long long)npx, s);
+        h->launches += 1;
+    }
+    h->order_buf = -1;
+    CK(cudaEventRecord(h->ev_packed[slot], s));
+    CK(cudaStreamWaitEvent(h->copy_stream, h->ev_packed[slot], 0));
+    if (left_rgb) CK(cudaMemcpyAsync(left_rgb, d_left, npx * 3, cudaMemcpyDeviceToHost, h->copy_stream));
+    if (disparity) CK(cudaMemcpyAsync(disparity, d_disp, npx * 2, cudaMemcpyDeviceToHost, h->copy_stream));
+    if (right_rgb) CK(cudaMemcpyAsync(right_rgb, d_right, npx * 3, cudaMemcpyDeviceToHost, h->copy_stream));
     CK(cudaEventRecord(h->ev_copied[slot], h->copy_stream));
     h->slot_busy[slot] = true;
     return 0;
@@ -596,6 +786,7 @@ int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_i
                        dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
     if (!dst_is_device) CK(cudaStreamSynchronize(s));
     h->frame_valid = false;
+    h->order_buf = -1;
     CK(cudaGetLastError());
     return 0;
 }

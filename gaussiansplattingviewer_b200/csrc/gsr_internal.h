@@ -27,7 +27,14 @@ struct FrameCounters {
     unsigned n_instances;  // D (sum of tiles touched), unclamped
     unsigned overflow;     // D > capacity
     unsigned n_sort;       // instances the tile sort handles: D, or 0 when the buffers overflowed
+    // not cleared per frame (pipelined paths read them at a later sync point and clear them there)
+    unsigned sticky_overflow;  // frames that overflowed since the last clear
+    unsigned sticky_max_d;     // largest D among them
 };
+
+// internal FrameParams.flags bit: the depth key is written for every Gaussian in front of the camera, visible or
+// not, so that one depth order serves several renders that share the view-space z (stereo capture)
+#define GSR_FLAG_INTERNAL_DEPTH_ALL 0x100u
 
 // Splat record, three float4 planes indexed by Gaussian:
 //   rec0 = (cx, cy, hx, hy)            splat centre (window coordinates) and 3-sigma half extents
@@ -112,6 +119,7 @@ void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* ins
                   float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s);
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s);
 void launch_extract_r(const float* rgba, float* r, long long n_px, cudaStream_t s);
+void launch_pack_disp_u16(const float* rgba, uint16_t* d, long long n_px, cudaStream_t s);
 void launch_keys64_from_ranges(const int2* ranges, int n_tiles, const uint32_t* gid, const uint32_t* depth_key,
                                uint64_t* out, cudaStream_t s);
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
@@ -123,3 +131,22 @@ void set_blend_skip(int v);
 void set_sort_small_tiles(int v);
 void set_sort_prefetch(int v);
 int measure_peaks_impl(float* fp32_tflops, float* ex2_tops, float* copy_gbs);
+
+// ---- PLY decode (ply_decode.cu) ----------------------------------------------------------------
+// Byte offsets of the 59 float32 columns load_ply reads, in canonical order:
+// 0-2 x y z | 3-5 f_dc_0..2 | 6-50 f_rest_0..44 | 51 opacity | 52-54 scale_0..2 | 55-58 rot_0..3
+struct PlyLayout {
+    int row_bytes;
+    int big_endian;
+    int off[59];
+};
+int ply_decode_configure(int row_bytes);  // 0 ok, -1 row too wide for the staging window
+void launch_ply_bbox_init(int* bbox_ord, cudaStream_t s);
+// rows: n vertex rows (device, 16-byte aligned, readable up to the next multiple of 16 bytes); outputs are
+// written at Gaussian index first + i
+void launch_ply_decode(const unsigned char* rows, const PlyLayout& lay, long long n, long long first, float* xyz,
+                       float4* rot4, float4* scale_op, float* sh, int* bbox_ord, int sm_count, cudaStream_t s);
+// bbox_ord: 10 words (6 ordered min/max, NaN mask, 3 running float32 sums); center chunks must be launched in row
+// order on one stream, each starting at a multiple of 4 rows
+void launch_ply_center(const float* xyz_rows, long long n_rows, int* bbox_ord, cudaStream_t s);
+void launch_ply_final(const int* bbox_ord, long long n, float* bbox6, float* center3, cudaStream_t s);

@@ -299,7 +299,12 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
                             ((conic0 * conic2 - conic1 * conic1) > 1e-5f * (conic0 * conic2));
             out.rec2[g] = make_float4(c0, c1, c2, pd ? 0.f : 1.f);
         }
-        out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
+        if (P.flags & GSR_FLAG_INTERNAL_DEPTH_ALL) {
+            const float d_all = -pv[2];
+            out.depth_key[g] = (d_all > 0.f) ? __float_as_uint(d_all) : 0xFFFFFFFFu;
+        } else {
+            out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
+        }
         out.trect[g] = trect;
         if (DEBUG) {
             float4* d = reinterpret_cast<float4*>(out.dbg_vsout + 16 * (size_t)g);

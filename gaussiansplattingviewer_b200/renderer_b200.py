@@ -116,6 +116,67 @@ class B200Renderer(GaussianRenderBase):
         _gsr.check(self._lib.gsr_set_gaussians(self._h, *[C.c_void_p(t.data_ptr()) for t in ts], n,
                                                int(ts[4].shape[1]), 1))
 
+    def load_ply(self, path):
+        """``load_ply(path)`` + ``update_gaussian_data`` in one step with the decode on the device
+        (/root/reference/util_gau.py:63-125 followed by renderer_ogl.py:132-137): the header is parsed
+        here, the vertex rows are read straight into pinned memory and ``gsr_load_ply_rows`` turns them
+        into the resident scene (activations bit-identical to the host ``util_gau.load_ply``).
+        Returns (bounding_box (2,3) float32, center (3,) float32) like the reference's second and third
+        results; ``download_gaussians()`` gives the GaussianData if the caller wants it on the host."""
+        torch = self._torch
+        with open(path, "rb") as f:
+            fmt, count, props = util_gau.read_ply_header(f)
+            row_bytes, offs = util_gau.ply_row_layout(props)
+            if fmt == "ascii":
+                rows = util_gau.read_ply_vertices(path).view(np.uint8)
+                big = 0
+            else:
+                big = 1 if fmt == "binary_big_endian" else 0
+                nbytes = count * row_bytes
+                pinned = torch.empty(max(nbytes, 1), dtype=torch.uint8, pin_memory=True)
+                rows = pinned.numpy()[:nbytes]
+                got = f.readinto(memoryview(rows)) if nbytes else 0
+                if got != nbytes:
+                    raise ValueError(f"{path}: truncated PLY body ({got} of {nbytes} bytes)")
+        bbox, center = self.load_ply_rows(rows, count, row_bytes, offs, big)
+        return bbox, center
+
+    def load_ply_rows(self, rows, count, row_bytes, offsets, big_endian=0):
+        """Vertex rows (a uint8 NumPy array on the host, or a uint8 CUDA tensor) -> resident scene."""
+        lay = _gsr.PlyLayout()
+        lay.row_bytes = int(row_bytes)
+        lay.big_endian = int(big_endian)
+        for i, o in enumerate(offsets):
+            lay.offset[i] = int(o)
+        bbox = np.zeros((2, 3), dtype=np.float32)
+        center = np.zeros(3, dtype=np.float32)
+        if isinstance(rows, np.ndarray):
+            ptr, on_dev = C.c_void_p(rows.ctypes.data), 0
+        else:
+            ptr, on_dev = C.c_void_p(rows.data_ptr()), 1
+        _gsr.check(self._lib.gsr_load_ply_rows(self._h, ptr, int(count), C.byref(lay), on_dev, _fptr(bbox),
+                                               _fptr(center), self._stream()))
+        self.gaussians = None
+        return bbox, center
+
+    def download_gaussians(self) -> util_gau.GaussianData:
+        """The resident scene as GaussianData (what OpenGLRenderer keeps in ``self.gaussians``)."""
+        st = self.stats()
+        n, shd = int(st.n_gaussians), 48
+        buf = C.c_void_p()
+        nb = C.c_longlong()
+        _gsr.check(self._lib.gsr_scene_buffer(self._h, 3, C.byref(buf), C.byref(nb)))
+        if n:
+            shd = int(nb.value // (4 * n))
+        xyz = np.empty((n, 3), np.float32)
+        rot = np.empty((n, 4), np.float32)
+        scale = np.empty((n, 3), np.float32)
+        op = np.empty((n, 1), np.float32)
+        sh = np.empty((n, shd), np.float32)
+        vp = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+        _gsr.check(self._lib.gsr_get_gaussians(self._h, vp(xyz), vp(rot), vp(scale), vp(op), vp(sh)))
+        return util_gau.GaussianData(xyz, rot, scale, op, sh)
+
     def _resolve_view(self, camera, use_file, pose):
         if use_file:
             return camera.get_view_matrix(True, pose["camera_front"], pose["camera_position"], pose["camera_up"],
@@ -221,6 +282,34 @@ class B200Renderer(GaussianRenderBase):
         buf = self._pinned_buf(("rgb8a", k), (self.h, self.w, 3), self._torch.uint8)
         _gsr.check(self._lib.gsr_render_rgb8_host_async(self._h, C.c_void_p(buf.data_ptr()), self._stream()))
         return buf.numpy()
+
+    def capture_stereo(self, pose_left, pose_right, want=("left", "disparity", "right"), share_order=True):
+        """One pose of the viewer's stereo capture (main.py:844-917): left RGB8, disparity uint16 (render_mod -1
+        at the left pose), right RGB8, packed on the device and copied to pinned host buffers while the next
+        pose renders.  ``pose_*`` are the dicts ``colmap.load_camera_positions`` returns (keys camera_view,
+        camera_position).  Returns {"left": (H,W,3) u8, "disparity": (H,W) u16, "right": (H,W,3) u8} views of
+        the buffers the images WILL land in: complete after the next-but-one call or ``sync_host()``."""
+        vl = _f32c(pose_left["camera_view"]).reshape(16)
+        cl = _f32c(np.asarray(pose_left["camera_position"], dtype=np.float32)[:3])
+        self._view, self._campos = vl.reshape(4, 4).copy(), cl.copy()  # update_camera_pose(poseLeft), main.py:848
+        self._push_state()
+        k = self._cap_k = getattr(self, "_cap_k", 0) ^ 1
+        out = {}
+        ptr = {"left": None, "disparity": None, "right": None}
+        for name, shape, dt in (("left", (self.h, self.w, 3), self._torch.uint8),
+                                ("disparity", (self.h, self.w), self._torch.int16),
+                                ("right", (self.h, self.w, 3), self._torch.uint8)):
+            if name in want:
+                buf = self._pinned_buf(("cap", name, k), shape, dt)
+                ptr[name] = C.c_void_p(buf.data_ptr())
+                a = buf.numpy()
+                out[name] = a.view(np.uint16) if name == "disparity" else a
+        vr = _f32c(pose_right["camera_view"]).reshape(16) if pose_right is not None else vl
+        cr = _f32c(np.asarray(pose_right["camera_position"], dtype=np.float32)[:3]) if pose_right is not None else cl
+        _gsr.check(self._lib.gsr_capture_stereo_async(self._h, _fptr(vl), _fptr(cl), _fptr(vr), _fptr(cr), ptr["left"],
+                                                      ptr["disparity"], ptr["right"], 1 if share_order else 0,
+                                                      self._stream()))
+        return out
 
     def sync_host(self):
         """Waits for every pipelined read-back."""

@@ -60,42 +60,87 @@ _PLY_TYPES = {
 }
 
 
+def read_ply_header(f):
+    """Parses a PLY header from the open binary file ``f`` (positioned at byte 0) and leaves ``f`` at
+    the first body byte.  Returns (format, vertex_count, [(property name, numpy type code), ...]) for the
+    FIRST element, the one load_ply reads (util_gau.py:66 ``plydata.elements[0]``)."""
+    if f.readline().strip() != b"ply":
+        raise ValueError("not a PLY file")
+    fmt = None
+    count = None
+    props = []
+    in_first = False
+    seen_first = False
+    while True:
+        line = f.readline()
+        if not line:
+            raise ValueError("unterminated PLY header")
+        tok = line.decode("ascii", "replace").split()
+        if not tok or tok[0] == "comment" or tok[0] == "obj_info":
+            continue
+        if tok[0] == "format":
+            fmt = tok[1]
+        elif tok[0] == "element":
+            if not seen_first:
+                count = int(tok[2])
+                in_first = True
+                seen_first = True
+            else:
+                in_first = False
+        elif tok[0] == "property" and in_first:
+            if tok[1] == "list":
+                raise ValueError("list properties are not supported")
+            props.append((tok[2], _PLY_TYPES[tok[1]]))
+        elif tok[0] == "end_header":
+            break
+    if fmt is None or count is None:
+        raise ValueError("incomplete PLY header")
+    return fmt, count, props
+
+
+PLY_COLUMNS = (["x", "y", "z"] + [f"f_dc_{i}" for i in range(3)] + [f"f_rest_{i}" for i in range(45)] +
+               ["opacity"] + [f"scale_{i}" for i in range(3)] + [f"rot_{i}" for i in range(4)])
+
+
+def ply_row_layout(props):
+    """(row_bytes, offsets[59]) of the columns load_ply reads, in the order of ``PLY_COLUMNS`` — the
+    table the device decoder (gsr_load_ply_rows) takes.  Columns are found by NAME and the numbered
+    families are ordered by their numeric suffix, like util_gau.py:92-112.  Raises AssertionError for a
+    file without exactly 45 ``f_rest_*`` (:94) and ValueError for a column that is not ``property float``."""
+    names = [n for n, _ in props]
+    offs = {}
+    o = 0
+    for n, t in props:
+        offs[n] = (o, t)
+        o += np.dtype(t).itemsize
+    row_bytes = o
+    extra = _numbered(names, "f_rest_")
+    assert len(extra) == 45
+    scale = _numbered(names, "scale_")
+    rot = _numbered(names, "rot")
+    if len(scale) != 3 or len(rot) != 4:
+        raise ValueError("expected 3 scale_* and 4 rot* properties")
+    cols = ["x", "y", "z", "f_dc_0", "f_dc_1", "f_dc_2"] + extra + ["opacity"] + scale + rot
+    out = []
+    for c in cols:
+        if c not in offs:
+            raise ValueError(f"PLY property {c} missing")
+        off, t = offs[c]
+        if t != "f4":
+            raise ValueError(f"PLY property {c} is not `property float`; use the host load_ply")
+        out.append(off)
+    return row_bytes, out
+
+
 def read_ply_vertices(path) -> np.ndarray:
     """Returns the first element of a PLY file as a NumPy structured array (one field per
     property).  Handles binary_little_endian, binary_big_endian and ascii; list properties are
     not supported (3DGS point clouds have none)."""
     with open(path, "rb") as f:
-        if f.readline().strip() != b"ply":
-            raise ValueError(f"{path}: not a PLY file")
-        fmt = None
-        count = None
-        props = []
-        in_first = False
-        seen_first = False
-        while True:
-            line = f.readline()
-            if not line:
-                raise ValueError(f"{path}: unterminated PLY header")
-            tok = line.decode("ascii", "replace").split()
-            if not tok or tok[0] == "comment" or tok[0] == "obj_info":
-                continue
-            if tok[0] == "format":
-                fmt = tok[1]
-            elif tok[0] == "element":
-                if not seen_first:
-                    count = int(tok[2])
-                    in_first = True
-                    seen_first = True
-                else:
-                    in_first = False
-            elif tok[0] == "property" and in_first:
-                if tok[1] == "list":
-                    raise ValueError(f"{path}: list properties are not supported")
-                props.append((tok[2], _PLY_TYPES[tok[1]]))
-            elif tok[0] == "end_header":
-                break
-        if fmt is None or count is None:
-            raise ValueError(f"{path}: incomplete PLY header")
+        try:
+            fmt, count, props = read_ply_header(f)
+        except ValueError as e:
+            raise ValueError(f"{path}: {e}") from e
         if fmt == "ascii":
             raw = np.loadtxt(f, dtype=np.float64, max_rows=count, ndmin=2)
             out = np.empty(count, dtype=[(n, "<" + t) for n, t in props])

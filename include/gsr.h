@@ -75,6 +75,28 @@ int gsr_version(void);
 int gsr_set_gaussians(gsr_t* h, const float* xyz, const float* rot, const float* scale, const float* opacity,
                       const float* sh, long long n, int sh_dim, int src_is_device);
 
+/* load_ply on the device (util_gau.py:63-125).  The host parses the PLY header (properties are looked up
+ * by NAME, :66-112) into byte offsets; the vertex rows are decoded by one kernel straight into the
+ * resident scene buffers: de-interleave, rot / ||rot|| and exp(scale) in float64 rounded to float32
+ * (:116-119), float32 sigmoid (:120-121, NumPy's float32 exp restated), f_rest channel-major ->
+ * coefficient-major (:99-100).  All 59 properties must be `property float`.
+ * offset[]: x y z | f_dc_0..2 | f_rest_0..44 | opacity | scale_0..2 | rot_0..3.
+ * rows: n * row_bytes bytes, HOST (pinned memory overlaps the upload with the decode, 64 MB chunks) or
+ * DEVICE (16-byte aligned, readable up to the next 16-byte boundary).
+ * bbox: xyz.min(axis=0), xyz.max(axis=0) (:81-83); center: xyz.mean(axis=0) with NumPy's float32 running
+ * sum (:85; a serial ~2 ns/vertex kernel — pass center = NULL to skip it).  Replaces the scene like
+ * gsr_set_gaussians (sh_dim 48).  Synchronises. */
+typedef struct {
+    int32_t row_bytes;
+    int32_t big_endian;
+    int32_t offset[59];
+} gsr_ply_layout;
+int gsr_load_ply_rows(gsr_t* h, const void* rows, long long n_vertices, const gsr_ply_layout* layout,
+                      int src_is_device, float bbox[6], float center[3], void* stream);
+/* inverse of gsr_set_gaussians: copies the resident scene into GaussianData's five host arrays (any may be
+ * NULL); what OpenGLRenderer keeps as self.gaussians (renderer_ogl.py:133).  Synchronises. */
+int gsr_get_gaussians(gsr_t* h, float* xyz, float* rot, float* scale, float* opacity, float* sh);
+
 /* replaces set_render_reso / glViewport (renderer_ogl.py:157-158, renderer_cuda.py:175-179) */
 int gsr_set_resolution(gsr_t* h, int width, int height);
 
@@ -114,6 +136,24 @@ int gsr_render_r32f_host(gsr_t* h, float* out_r_host, void* stream);
  * instance buffers the sync point grows them and returns GSR_EOVERFLOW: submit that frame again. */
 int gsr_render_rgb8_host_async(gsr_t* h, uint8_t* out_rgb_host, void* stream);
 int gsr_host_sync(gsr_t* h);
+
+/* One pose of the stereo capture loop (main.py:844-917; one of the ~100 poses per scene of render_all.py:14-35),
+ * three renders and their packing on the device:
+ *   left      : scale/render_mod of gsr_set_params at (view_left, campos_left) on an RGB8 target ->
+ *               H*W*3 bytes, glReadPixels(GL_RGB, GL_UNSIGNED_BYTE) + FLIP_TOP_BOTTOM (:846-852, :912)
+ *   disparity : render_mod -1 (1.2x scale, gau_vert.glsl:151-156,182-211) at the LEFT pose on the R32F target
+ *               (:858-870) -> H*W uint16 = (d * 65535).astype(uint16) (:878-879); the rotate-180 + mirror of
+ *               :880-881 is the top-down row order every image of this ABI already has
+ *   right     : like left at (view_right, campos_right) (:888-897); the reference builds view_right as the left
+ *               view pre-multiplied by an x translation of -0.5 in view space (:376-380)
+ * Any of the three host pointers may be NULL to skip that render.  share_order != 0: the depth order is
+ * computed once per call and reused by the other renders when their view-space depths are identical (same
+ * third row of the view matrix) — the result is bit-identical to three independent frames.
+ * Pipelined exactly like gsr_render_rgb8_host_async (same two slots, same gsr_host_sync / GSR_EOVERFLOW
+ * rules); host buffers should be pinned. */
+int gsr_capture_stereo_async(gsr_t* h, const float view_left[16], const float campos_left[3],
+                             const float view_right[16], const float campos_right[3], uint8_t* left_rgb_host,
+                             uint16_t* disparity_host, uint8_t* right_rgb_host, int share_order, void* stream);
 
 /* The render_all.py workload (render_all.py:14-35, main.py:793-840): n_views poses over one scene.
  * views: n_views x 16 floats, campos: n_views x 3 floats (HOST).  out_rgba: DEVICE buffer of
@@ -159,7 +199,7 @@ int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* c
 #define GSR_TUNE_BLEND_PPT 0
 #define GSR_TUNE_SORT_SMALL_TILES 1
 #define GSR_TUNE_BLEND_SHAPE8 2 /* 1 = a warp owns an 8-column block instead of 16 columns (main mode only) */
-#define GSR_TUNE_SORT_PREFETCH 4 /* 1 = radix passes prefetch the next tile with cp.async (32-bit keys) */
+#define GSR_TUNE_SORT_PREFETCH 4 /* 1 (default) = 32-bit-key radix passes use super-tiles: two 4096-key sub-tiles per look-back */
 #define GSR_TUNE_BLEND_SKIP 3   /* 1 = warp-level skip of quads that miss all of the warp's live pixels */
 int gsr_tune(gsr_t* h, int key, int value);
 

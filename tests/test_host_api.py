@@ -122,3 +122,18 @@ def test_trajectory_poses(golden):
     # the loop passes through the (scaled) csv positions
     v18, p18 = scenes.trajectory_poses(rows, 18)
     assert np.allclose(p18, rows[:, 6:9] * 3.0, atol=1e-5)
+
+
+def test_ply_row_layout_finds_columns_by_name():
+    # the table the device decoder takes: offsets in PLY_COLUMNS order, whatever the file order is
+    names = ["rot_3", "x", "nx", "z", "y"] + [f"f_rest_{i}" for i in reversed(range(45))] + \
+            ["f_dc_2", "f_dc_0", "f_dc_1", "opacity", "scale_2", "scale_0", "scale_1", "rot_0", "rot_2", "rot_1"]
+    props = [(n, "f4") for n in names]
+    row_bytes, offs = util_gau.ply_row_layout(props)
+    assert row_bytes == 4 * len(names) and len(offs) == 59 == len(util_gau.PLY_COLUMNS)
+    for col, off in zip(util_gau.PLY_COLUMNS, offs):
+        assert names[off // 4] == col
+    with pytest.raises(AssertionError):  # /root/reference/util_gau.py:94
+        util_gau.ply_row_layout([p for p in props if p[0] != "f_rest_7"])
+    with pytest.raises(ValueError):
+        util_gau.ply_row_layout([(n, "f8" if n == "opacity" else t) for n, t in props])
