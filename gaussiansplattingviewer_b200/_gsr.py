@@ -66,6 +66,8 @@ SIGNATURES = {
     "gsr_capture_stereo_async": (C.c_int, [_vp, _fp, _fp, _fp, _fp, _vp, _vp, _vp, C.c_int, _vp]),
     "gsr_render_batch": (C.c_int, [_vp, _fp, _fp, C.c_int, _vp, _vp]),
     "gsr_sort_depth": (C.c_int, [_vp, _fp, _vp, C.c_int, _vp]),
+    "gsr_freeze_order": (C.c_int, [_vp, _fp, _vp]),
+    "gsr_thaw_order": (C.c_int, [_vp]),
     "gsr_sort_pairs": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int, _vp]),
     "gsr_get_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
     "gsr_debug_fetch": (C.c_int, [_vp, C.c_int, _vp, _ll, C.POINTER(_ll)]),

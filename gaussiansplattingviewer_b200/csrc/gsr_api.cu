@@ -77,7 +77,8 @@ struct gsr_renderer {
     // pipelined read-back: second RGB8 buffer, copy stream, per-slot events
     uint8_t* d_rgb8b = nullptr;
     uint8_t* d_cap[2] = {nullptr, nullptr};  // stereo capture slots: left RGB8 | right RGB8 | disparity u16
-    int order_buf = -1;                      // d_gid[] buffer holding a shared depth order (stereo capture)
+    int order_buf = -1;                      // d_gid[] buffer holding a shared depth order (stereo capture, frozen order)
+    bool order_frozen = false;               // gsr_freeze_order: frames draw in the stored order
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_packed[2] = {}, ev_copied[2] = {};
     bool slot_busy[2] = {false, false};
@@ -146,6 +147,7 @@ int alloc_gaussian_buffers(gsr_t* h, long long n, int sh_dim) {
     h->sh_dim = sh_dim;
     h->frame_valid = false;
     h->order_buf = -1;
+    h->order_frozen = false;
     return 0;
 }
 
@@ -199,7 +201,11 @@ int tile_bits(int n_tiles) {
 // remember the order; 2 = reuse the remembered order (same view-space depths: same view up to an in-plane shift)
 int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode = 0) {
     FrameParams fp = fp_in;
-    if (fp.flags & GSR_FLAG_KEYS64) order_mode = 0;
+    if (fp.flags & GSR_FLAG_KEYS64) {
+        if (h->order_frozen) return fail(GSR_EINVAL, "a frozen order needs the two-level sort (clear GSR_FLAG_KEYS64)");
+        order_mode = 0;
+    }
+    if (h->order_frozen) order_mode = 2;
     if (order_mode == 2 && h->order_buf < 0) order_mode = 1;
     fp.flags &= ~GSR_FLAG_INTERNAL_DEPTH_ALL;
     if (order_mode == 1) fp.flags |= GSR_FLAG_INTERNAL_DEPTH_ALL;
@@ -734,7 +740,7 @@ int gsr_capture_stereo_async(gsr_t* h, const float view_left[16], const float ca
         launch_pack_rgb8(h->d_frame, d_right, (long long)npx, s);
         h->launches += 1;
     }
-    h->order_buf = -1;
+    if (!h->order_frozen) h->order_buf = -1;
     CK(cudaEventRecord(h->ev_packed[slot], s));
     CK(cudaStreamWaitEvent(h->copy_stream, h->ev_packed[slot], 0));
     if (left_rgb) CK(cudaMemcpyAsync(left_rgb, d_left, npx * 3, cudaMemcpyDeviceToHost, h->copy_stream));
@@ -787,7 +793,36 @@ int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_i
     if (!dst_is_device) CK(cudaStreamSynchronize(s));
     h->frame_valid = false;
     h->order_buf = -1;
+    h->order_frozen = false;
     CK(cudaGetLastError());
+    return 0;
+}
+
+// The OpenGL backend draws in the order of the LAST sort_and_update, whatever the camera has done since
+// (renderer_ogl.py:139-146; main.py:989-997: a "sort" button, or every frame when "auto sort" is ticked).
+int gsr_freeze_order(gsr_t* h, const float view[16], void* stream) {
+    if (!h || !view) return fail(GSR_EINVAL, "null argument");
+    if (!h->d_xyz) return fail(GSR_EINVAL, "no gaussians set");
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long N = h->N;
+    h->order_buf = 0;
+    h->order_frozen = true;
+    h->frame_valid = false;
+    if (N == 0) return 0;
+    launch_depth_keys(h->d_xyz, view, h->d_dkey[0], N, s, 1);
+    h->launches += 1;
+    SortOptions so_n = {0, false, false, 0x3u};
+    h->order_buf = radix_sort_pairs<uint32_t>(h->d_dkey[0], h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1], true, N,
+                                              nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int gsr_thaw_order(gsr_t* h) {
+    if (!h) return fail(GSR_EINVAL, "null handle");
+    h->order_frozen = false;
+    h->order_buf = -1;
     return 0;
 }
 

@@ -103,7 +103,7 @@ void launch_pack_scene(const float* rot, const float* scale, const float* opacit
                        long long n, cudaStream_t s);
 void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
                        long long n, int sh_dim, cudaStream_t s);
-void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s);
+void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s, int negate = 0);
 // big_list: N uint4 entries, big_count: one zeroed counter (large rectangles, see binning.cu)
 void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, SplatBuffers sp,
                              FrameCounters* counters, uint32_t* chain_status, uint32_t* chain_ticket,

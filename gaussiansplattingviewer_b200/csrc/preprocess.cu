@@ -345,7 +345,7 @@ __global__ void k_pack_scene(const float* __restrict__ rot, const float* __restr
 // keys for the global far->near order of sort_and_update: ascending view z, -0 == +0, NaN last
 // (/root/reference/renderer_ogl.py:10-19; oracle/gs_oracle.c f32_sort_key)
 struct View16 { float m[16]; };
-__global__ void k_depth_keys(const float* __restrict__ xyz, View16 vm, uint32_t* __restrict__ keys, long long n) {
+__global__ void k_depth_keys(const float* __restrict__ xyz, View16 vm, uint32_t* __restrict__ keys, long long n, int negate) {
     const float* view = vm.m;
     const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= n) return;
@@ -354,6 +354,7 @@ __global__ void k_depth_keys(const float* __restrict__ xyz, View16 vm, uint32_t*
     uint32_t k;
     if (d != d) k = 0xFFFFFFFFu;
     else {
+        if (negate) d = -d;  // ascending depth = -z: the front-to-back order the tile lists are built in
         d = d + 0.0f;
         const uint32_t u = __float_as_uint(d);
         k = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
@@ -387,9 +388,9 @@ void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers o
     }
 }
 
-void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s) {
+void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s, int negate) {
     if (n <= 0) return;
     View16 vm;
     for (int i = 0; i < 16; ++i) vm.m[i] = view16_host[i];
-    k_depth_keys<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(xyz, vm, keys, n);
+    k_depth_keys<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(xyz, vm, keys, n, negate);
 }

@@ -76,6 +76,7 @@ class B200Renderer(GaussianRenderBase):
         self.render_mod = 3
         self.is_depth_image = 0
         self.keys64 = bool(keys64)
+        self.auto_sort = True
         self.debug = False
         self.target_unorm = None  # None: unorm (clamped) target except in render_mod -1 (R32F FBO, main.py:866-870)
         self._view = None
@@ -184,12 +185,23 @@ class B200Renderer(GaussianRenderBase):
         return camera.get_view_matrix(True)
 
     def sort_and_update(self, camera: util.Camera = None, use_file=False, pose=None):
-        # renderer_ogl.py:139-146.  draw() depth-sorts per tile for the CURRENT view every frame (as the
-        # CUDA backend does, renderer_cuda.py:139-140), so no order needs uploading; the view is kept so
-        # gaussian_order() can produce the `gi` buffer the OpenGL backend would have uploaded.
+        """renderer_ogl.py:139-146.  With ``auto_sort`` True (default; the viewer's "auto sort" box, main.py:993-997)
+        draw() depth-sorts for the CURRENT view every frame, as the CUDA backend does (renderer_cuda.py:139-140),
+        and this call only records the view for ``gaussian_order()``.  With ``auto_sort`` False the call freezes
+        the depth order of this view on the device (gsr_freeze_order) and draw() keeps using it until the next
+        sort_and_update, which is what the OpenGL backend does between presses of "sort Gaussians"."""
         if camera is not None:
             self._sort_view = _f32c(self._resolve_view(camera, use_file, pose))
+        if not self.auto_sort and self._sort_view is not None:
+            _gsr.check(self._lib.gsr_freeze_order(self._h, _fptr(self._sort_view.reshape(16)), self._stream()))
+            self._frozen = True
         return
+
+    def set_auto_sort(self, on: bool):
+        self.auto_sort = bool(on)
+        if self.auto_sort and getattr(self, "_frozen", False):
+            _gsr.check(self._lib.gsr_thaw_order(self._h))
+            self._frozen = False
 
     def gaussian_order(self, view=None, to_host=True):
         """The OpenGL backend's `gi` buffer: int32 (N, 1), ascending view-space z (far -> near), stable

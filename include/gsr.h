@@ -167,6 +167,16 @@ int gsr_render_batch(gsr_t* h, const float* views, const float* campos, int n_vi
  * stable, NaN last; N int32, host (dst_is_device = 0, synchronises) or device memory. */
 int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_is_device, void* stream);
 
+/* sort_and_update WITHOUT auto-sort (renderer_ogl.py:139-146 as driven by main.py:989-997: the order buffer `gi`
+ * is rebuilt only when "sort Gaussians" is pressed or "auto sort" is ticked, and draw() keeps using it while the
+ * camera moves).  gsr_freeze_order sorts the N Gaussians by their depth in `view` once (stable, front to back,
+ * Gaussians behind that camera first — the reverse of the far->near argsort the reference uploads); every later
+ * frame skips its own depth sort and builds its tile lists in that order (culling, footprints and colours still
+ * follow the frame's own camera, exactly like the vertex shader reading a stale `gi`).  gsr_thaw_order, a new
+ * scene or gsr_sort_depth return to one depth sort per frame.  Not available with GSR_FLAG_KEYS64. */
+int gsr_freeze_order(gsr_t* h, const float view[16], void* stream);
+int gsr_thaw_order(gsr_t* h);
+
 /* The onesweep LSB radix sort primitive on its own (device pointers, n pairs, stable, bits
  * [begin_bit, end_bit) of the key).  key_bits is 32 or 64; values are uint32.  Sorted data ends up in
  * keys/vals; keys_tmp/vals_tmp are scratch of the same size.  vals may be NULL on input to mean
