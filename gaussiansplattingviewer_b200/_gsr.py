@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "csrc", "libgsr.so")
 GSR_FLAG_CLAMP_UNORM = 1
 GSR_FLAG_KEYS64 = 2
 GSR_FLAG_DEBUG = 4
+GSR_FLAG_OFFICIAL = 8
 
 GSR_DBG_VSOUT = 0
 GSR_DBG_SETUP = 1

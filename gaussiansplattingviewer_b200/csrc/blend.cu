@@ -39,7 +39,11 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// MODE: 0 = gaussian falloff (render_mod >= 0 or -1), 2 = billboard (-2), 3 = flat ball (-3), 4 = gaussian ball (-4)
+// MODE: 0 = gaussian falloff (render_mod >= 0 or -1), 2 = billboard (-2), 3 = flat ball (-3), 4 = gaussian ball (-4),
+// 5 = the official rasterizer's renderCUDA rule (GSR_FLAG_OFFICIAL; diff_gaussian_rasterization forward.cu, the
+// kernel renderer_cuda.py:212-224 calls): pixel coordinates are integers, rows run top-down, every pixel of a
+// touched tile evaluates the splat (the record carries infinite half extents), `power > 0` is always tested, a
+// pixel stops BEFORE blending the splat that would take T * (1 - alpha) below 1e-4, and alpha is written as 1.
 template <int MODE, int PPT, bool COUNT, bool SHAPE8, bool SKIP>
 __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
                                                      const uint32_t* __restrict__ inst_gid, SplatBuffers sp,
@@ -66,11 +70,12 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
     }
     const int px = blockIdx.x * GSR_TILE + lx;
     const int py0 = blockIdx.y * GSR_TILE + lyb * PPT;  // GL row, 0 = bottom
-    const float pxf = (float)px + 0.5f;
+    constexpr float CENTRE = (MODE == 5) ? 0.f : 0.5f;
+    const float pxf = (float)px + CENTRE;
     float pyf[PPT], T[PPT], cr[PPT], cg[PPT], cb[PPT];
 #pragma unroll
     for (int k = 0; k < PPT; ++k) {
-        pyf[k] = (float)(py0 + k) + 0.5f;
+        pyf[k] = (float)(py0 + k) + CENTRE;
         // pixels outside the image start terminated
         T[k] = (px < W && py0 + k < H) ? 1.f : 0.f;
         cr[k] = cg[k] = cb[k] = 0.f;
@@ -172,7 +177,15 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                         const float alpha = fminf(0.99f, q.w * e);
                         valid = valid && !(alpha < 1.f / 255.f);
                         if (CHECK_POWER) valid = valid && !(p2 > 0.f);
-                        if (MODE == 0) {
+                        if (MODE == 5) {
+                            const float test_T = T[k] * (1.f - alpha);
+                            const bool stop = valid && (test_T < 0.0001f);
+                            const bool hit = valid && !stop;
+                            if (COUNT) n_hit += hit ? 1u : 0u;
+                            const float w = hit ? alpha * T[k] : 0.f;
+                            cr[k] = fmaf(w, c.x, cr[k]); cg[k] = fmaf(w, c.y, cg[k]); cb[k] = fmaf(w, c.z, cb[k]);
+                            T[k] = stop ? 0.f : (hit ? test_T : T[k]);
+                        } else if (MODE == 0) {
                             if (COUNT) n_hit += valid ? 1u : 0u;
                             const float w = valid ? alpha * T[k] : 0.f;
                             cr[k] = fmaf(w, c.x, cr[k]); cg[k] = fmaf(w, c.y, cg[k]); cb[k] = fmaf(w, c.z, cb[k]);
@@ -207,8 +220,9 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
 #pragma unroll
     for (int k = 0; k < PPT; ++k) {
         if (!outside[k]) {
-            float4* o = reinterpret_cast<float4*>(out_rgba) + (size_t)(H - 1 - (py0 + k)) * (size_t)W + px;
-            *o = make_float4(cr[k], cg[k], cb[k], 1.f - T[k]);
+            const int row = (MODE == 5) ? (py0 + k) : (H - 1 - (py0 + k));
+            float4* o = reinterpret_cast<float4*>(out_rgba) + (size_t)row * (size_t)W + px;
+            *o = make_float4(cr[k], cg[k], cb[k], (MODE == 5) ? 1.f : 1.f - T[k]);
         }
     }
     if (COUNT) {
@@ -270,7 +284,8 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
     const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
     constexpr int TH = 256 / BL_PPT;
 #define BL_ARGS fp, ranges, inst_gid, sp, out_rgba, flags, pc
-    if (render_mod == -2) k_blend<2, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
+    if (flags & GSR_FLAG_OFFICIAL_BIT) k_blend<5, BL_PPT, COUNT, BL_SHAPE8, false><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (render_mod == -2) k_blend<2, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
     else if (render_mod == -3) k_blend<3, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
     else if (render_mod == -4) k_blend<4, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
     else if (COUNT) k_blend<0, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);

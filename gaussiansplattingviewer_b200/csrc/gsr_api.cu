@@ -208,6 +208,26 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     if (h->order_frozen) order_mode = 2;
     if (order_mode == 2 && h->order_buf < 0) order_mode = 1;
     fp.flags &= ~GSR_FLAG_INTERNAL_DEPTH_ALL;
+    const bool official = (fp.flags & GSR_FLAG_OFFICIAL) != 0;
+    if (official) {
+        // what CUDARenderer.update_camera_pose builds (renderer_cuda.py:181-194): view rows 0 and 2 negated
+        // (GL -> z-forward), projmatrix = P_gl * view; the kernels read them from fp.view / fp.proj
+        if (h->order_frozen) return fail(GSR_EINVAL, "the official-rasterizer mode sorts every frame (thaw the order first)");
+        order_mode = 0;
+        float vo[16], po[16];
+        for (int r = 0; r < 4; ++r)
+            for (int c = 0; c < 4; ++c) vo[r * 4 + c] = (r == 0 || r == 2) ? -fp_in.view[r * 4 + c] : fp_in.view[r * 4 + c];
+        for (int r = 0; r < 4; ++r)
+            for (int c = 0; c < 4; ++c) {
+                float acc = fp_in.proj[r * 4 + 0] * vo[0 * 4 + c];
+                acc = acc + fp_in.proj[r * 4 + 1] * vo[1 * 4 + c];
+                acc = acc + fp_in.proj[r * 4 + 2] * vo[2 * 4 + c];
+                acc = acc + fp_in.proj[r * 4 + 3] * vo[3 * 4 + c];
+                po[r * 4 + c] = acc;
+            }
+        memcpy(fp.view, vo, 64);
+        memcpy(fp.proj, po, 64);
+    }
     if (order_mode == 1) fp.flags |= GSR_FLAG_INTERNAL_DEPTH_ALL;
     if (h->N <= 0 && !h->d_xyz) return fail(GSR_EINVAL, "no gaussians set");
     if (h->W <= 0) return fail(GSR_EINVAL, "no resolution set");
@@ -235,7 +255,8 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     if (timed) cudaEventRecord(h->ev[0], s);
     launch_set_params(h->d_fp, fp, h->d_counters, s);
     CK(cudaMemsetAsync(h->d_tile_grid, 0, sizeof(int) * (size_t)sp.grid_stride * GSR_GRID_REPLICAS, s));
-    launch_preprocess(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
+    if (official) launch_preprocess_official(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
+    else launch_preprocess(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     h->launches += 2;
     if (timed) cudaEventRecord(h->ev[1], s);
     CK(cudaMemsetAsync(h->d_chain, 0, h->chain_bytes, s));

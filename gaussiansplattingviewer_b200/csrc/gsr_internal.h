@@ -35,6 +35,7 @@ struct FrameCounters {
 // internal FrameParams.flags bit: the depth key is written for every Gaussian in front of the camera, visible or
 // not, so that one depth order serves several renders that share the view-space z (stereo capture)
 #define GSR_FLAG_INTERNAL_DEPTH_ALL 0x100u
+#define GSR_FLAG_OFFICIAL_BIT 8u  // == GSR_FLAG_OFFICIAL of include/gsr.h
 
 // Splat record, three float4 planes indexed by Gaussian:
 //   rec0 = (cx, cy, hx, hy)            splat centre (window coordinates) and 3-sigma half extents
@@ -103,6 +104,9 @@ void launch_pack_scene(const float* rot, const float* scale, const float* opacit
                        long long n, cudaStream_t s);
 void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
                        long long n, int sh_dim, cudaStream_t s);
+// official-rasterizer semantics: fp->view / fp->proj hold the z-forward view and the FULL projection (P * view)
+void launch_preprocess_official(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
+                                long long n, int sh_dim, cudaStream_t s);
 void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s, int negate = 0);
 // big_list: N uint4 entries, big_count: one zeroed counter (large rectangles, see binning.cu)
 void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, SplatBuffers sp,

@@ -326,6 +326,198 @@ __global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restric
     if (threadIdx.x == 0 && s_visible) atomicAdd(&counters->n_visible, s_visible);
 }
 
+// ---- official-rasterizer semantics (GSR_FLAG_OFFICIAL) ---------------------------------------------------
+// What CUDARenderer.draw hands to diff_gaussian_rasterization (/root/reference/renderer_cuda.py:181-228): the
+// package is NOT in the reference tree and not pinned (README.md:29), so this restates the published forward
+// pass (preprocessCUDA / computeCov2D / computeColorFromSH / getRect of graphdeco-inria/diff-gaussian-rasterization,
+// the pre-antialiasing revision whose call returns (color, radii)) — parity unpinned, checked against the CPU
+// restatement in oracle/gs_oracle.c only.  Differences from the shader path: cull is view z <= 0.2 only; the
+// footprint is every tile overlapping the square of radius ceil(3 sqrt(lambda_max)) around the pixel position
+// ((ndc + 1) S - 1) / 2 (tiles anchored at the TOP-left, rows top-down because the viewer negates view rows 0 and
+// 2); colour is clamped below at 0 only; the full SH degree of the scene is used whatever render_mod says
+// (renderer_cuda.py:137, set_render_mod is a no-op :145-146).  P.view is the z-forward view, P.proj = P_gl * view.
+template <bool DEBUG>
+__global__ void __launch_bounds__(256) k_preprocess_official(const FrameParams* __restrict__ fp, SceneBuffers scene,
+                                                             SplatBuffers out, FrameCounters* __restrict__ counters,
+                                                             unsigned n, int sh_dim) {
+    __shared__ SharedParams P;
+    __shared__ unsigned s_visible;
+    if (threadIdx.x < 16) { P.view[threadIdx.x] = fp->view[threadIdx.x]; P.proj[threadIdx.x] = fp->proj[threadIdx.x]; }
+    if (threadIdx.x == 32) {
+        P.htanx = fp->htanx; P.htany = fp->htany; P.focal = fp->focal;
+        P.campos[0] = fp->campos[0]; P.campos[1] = fp->campos[1]; P.campos[2] = fp->campos[2];
+        P.scale_modifier = fp->scale_modifier; P.render_mod = fp->render_mod;
+        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.tiles_y = fp->tiles_y; P.flags = fp->flags;
+        s_visible = 0;
+    }
+    __syncthreads();
+    const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
+    bool ok = false;
+    if (g < n) {
+        float vs[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) vs[k] = 0.f;
+        int rminx = 0, rmaxx = 0, rminy = 0, rmaxy = 0;
+        float pix = 0.f, piy = 0.f, depth = 0.f;
+        float conic0 = 0.f, conic1 = 0.f, conic2 = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f, opac = 0.f;
+        const float px = __ldg(scene.xyz + 3 * (size_t)g + 0);
+        const float py = __ldg(scene.xyz + 3 * (size_t)g + 1);
+        const float pz = __ldg(scene.xyz + 3 * (size_t)g + 2);
+        const float g_pos[4] = {px, py, pz, 1.f};
+        float pv[4];
+        mat4_mul_vec4(P.view, g_pos, pv);          // transformPoint4x3
+        if (pv[2] > 0.2f) {                        // in_frustum: p_view.z <= 0.2f -> culled
+            float ph[4];
+            mat4_mul_vec4(P.proj, g_pos, ph);      // transformPoint4x4 with the full projection
+            const float p_w = 1.0f / (ph[3] + 0.0000001f);
+            const float pp0 = ph[0] * p_w, pp1 = ph[1] * p_w, pp2 = ph[2] * p_w;
+            const float4 q = __ldg(scene.rot + g);
+            const float4 so = __ldg(scene.scale_op + g);
+            // computeCov3D
+            m3 S;
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int r = 0; r < 3; ++r) S.m[c][r] = 0.f;
+            S.m[0][0] = P.scale_modifier * so.x; S.m[1][1] = P.scale_modifier * so.y; S.m[2][2] = P.scale_modifier * so.z;
+            const float r = q.x, x = q.y, y = q.z, z = q.w;
+            m3 R;
+            R.m[0][0] = 1.f - 2.f * (y * y + z * z); R.m[0][1] = 2.f * (x * y - r * z); R.m[0][2] = 2.f * (x * z + r * y);
+            R.m[1][0] = 2.f * (x * y + r * z); R.m[1][1] = 1.f - 2.f * (x * x + z * z); R.m[1][2] = 2.f * (y * z - r * x);
+            R.m[2][0] = 2.f * (x * z - r * y); R.m[2][1] = 2.f * (y * z + r * x); R.m[2][2] = 1.f - 2.f * (x * x + y * y);
+            const m3 M = m3_mul(S, R);
+            const m3 cov3d = m3_mul(m3_transpose(M), M);
+            // computeCov2D
+            const float focal_x = (float)P.W / (2.0f * P.htanx), focal_y = (float)P.H / (2.0f * P.htany);
+            float tx = pv[0], ty = pv[1];
+            const float tz = pv[2];
+            const float limx = 1.3f * P.htanx, limy = 1.3f * P.htany;
+            const float txtz = tx / tz, tytz = ty / tz;
+            tx = gl_min(limx, gl_max(-limx, txtz)) * tz;
+            ty = gl_min(limy, gl_max(-limy, tytz)) * tz;
+            m3 J;
+            J.m[0][0] = focal_x / tz; J.m[0][1] = 0.0f; J.m[0][2] = -(focal_x * tx) / (tz * tz);
+            J.m[1][0] = 0.0f; J.m[1][1] = focal_y / tz; J.m[1][2] = -(focal_y * ty) / (tz * tz);
+            J.m[2][0] = 0.f; J.m[2][1] = 0.f; J.m[2][2] = 0.f;
+            m3 Wm;
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int rr = 0; rr < 3; ++rr) Wm.m[c][rr] = P.view[c * 4 + rr];
+            const m3 T = m3_mul(Wm, J);
+            const m3 A = m3_mul(m3_transpose(T), m3_transpose(cov3d));
+            m3 cov = m3_mul(A, T);
+            cov.m[0][0] += 0.3f;
+            cov.m[1][1] += 0.3f;
+            const float ca = cov.m[0][0], cb = cov.m[0][1], cc = cov.m[1][1];
+            const float det = (ca * cc - cb * cb);
+            if (det != 0.0f) {
+                const float det_inv = 1.f / det;
+                conic0 = cc * det_inv; conic1 = -cb * det_inv; conic2 = ca * det_inv;
+                const float mid = 0.5f * (ca + cc);
+                const float disc = sqrtf(gl_max(0.1f, mid * mid - det));
+                const float lambda1 = mid + disc, lambda2 = mid - disc;
+                const float my_radius = ceilf(3.f * sqrtf(gl_max(lambda1, lambda2)));
+                // ndc2Pix: ((v + 1.0) * S - 1.0) * 0.5 is evaluated in double (the literals are doubles)
+                pix = (float)((((double)pp0 + 1.0) * (double)P.W - 1.0) * 0.5);
+                piy = (float)((((double)pp1 + 1.0) * (double)P.H - 1.0) * 0.5);
+                if (finitef(pix) && finitef(piy) && finitef(my_radius)) {
+                    // getRect (BLOCK_X = BLOCK_Y = 16); the casts are clamped first so they stay defined
+                    const float lim = 1.0e9f;
+                    const float ax = gl_min(lim, gl_max(-lim, (pix - my_radius) / 16.f));
+                    const float bx = gl_min(lim, gl_max(-lim, (pix + my_radius + 15.f) / 16.f));
+                    const float ay = gl_min(lim, gl_max(-lim, (piy - my_radius) / 16.f));
+                    const float by = gl_min(lim, gl_max(-lim, (piy + my_radius + 15.f) / 16.f));
+                    rminx = min(P.tiles_x, max(0, (int)ax)); rmaxx = min(P.tiles_x, max(0, (int)bx));
+                    rminy = min(P.tiles_y, max(0, (int)ay)); rmaxy = min(P.tiles_y, max(0, (int)by));
+                    ok = ((rmaxx - rminx) * (rmaxy - rminy) != 0);
+                }
+                // computeColorFromSH at the scene's full degree
+                float dx = px - P.campos[0], dy = py - P.campos[1], dz = pz - P.campos[2];
+                const float len = sqrtf((dx * dx + dy * dy) + dz * dz);
+                dx = dx / len; dy = dy / len; dz = dz / len;
+                const float* __restrict__ shp = scene.sh + (size_t)sh_dim * (size_t)g;
+                int ncoef = 1;
+                if (sh_dim > 3) ncoef = 4;
+                if (sh_dim > 12) ncoef = 9;
+                if (sh_dim > 27) ncoef = 16;
+                float c[3];
+#define SHV(k, ch) __ldg(shp + (k) * 3 + (ch))
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) c[ch] = SH_C0 * SHV(0, ch);
+                if (ok && ncoef >= 4) {
+                    const float X = dx, Y = dy, Z = dz;
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch)
+                        c[ch] = c[ch] - SH_C1 * Y * SHV(1, ch) + SH_C1 * Z * SHV(2, ch) - SH_C1 * X * SHV(3, ch);
+                    if (ncoef >= 9) {
+                        const float xx = X * X, yy = Y * Y, zz = Z * Z;
+                        const float xy = X * Y, yz = Y * Z, xz = X * Z;
+#pragma unroll
+                        for (int ch = 0; ch < 3; ++ch)
+                            c[ch] = c[ch] + SH_C2_0 * xy * SHV(4, ch) + SH_C2_1 * yz * SHV(5, ch) +
+                                    SH_C2_2 * (2.0f * zz - xx - yy) * SHV(6, ch) + SH_C2_3 * xz * SHV(7, ch) +
+                                    SH_C2_4 * (xx - yy) * SHV(8, ch);
+                        if (ncoef >= 16) {
+#pragma unroll
+                            for (int ch = 0; ch < 3; ++ch)
+                                c[ch] = c[ch] + SH_C3_0 * Y * (3.0f * xx - yy) * SHV(9, ch) + SH_C3_1 * xy * Z * SHV(10, ch) +
+                                        SH_C3_2 * Y * (4.0f * zz - xx - yy) * SHV(11, ch) +
+                                        SH_C3_3 * Z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SHV(12, ch) +
+                                        SH_C3_4 * X * (4.0f * zz - xx - yy) * SHV(13, ch) +
+                                        SH_C3_5 * Z * (xx - yy) * SHV(14, ch) + SH_C3_6 * X * (xx - 3.0f * yy) * SHV(15, ch);
+                        }
+                    }
+                }
+#undef SHV
+                c0 = gl_max(c[0] + 0.5f, 0.f); c1 = gl_max(c[1] + 0.5f, 0.f); c2 = gl_max(c[2] + 0.5f, 0.f);
+                opac = so.w;
+                depth = pv[2];
+                if (DEBUG && ok) {
+                    vs[0] = 1.f; vs[1] = pp0; vs[2] = pp1; vs[3] = pp2; vs[4] = my_radius; vs[5] = my_radius;
+                    vs[6] = conic0; vs[7] = conic1; vs[8] = conic2; vs[9] = c0; vs[10] = c1; vs[11] = c2;
+                    vs[12] = opac; vs[13] = depth;
+                }
+            }
+        }
+        uint2 trect = make_uint2(0u, 0u);
+        if (ok) {
+            trect.x = (unsigned)rminx | ((unsigned)(rmaxx - rminx) << 16);
+            trect.y = (unsigned)rminy | ((unsigned)(rmaxy - rminy) << 16);
+            if (out.tile_grid) {
+                const int gw = out.grid_w;
+                int* grid = out.tile_grid + (size_t)(blockIdx.x & (GSR_GRID_REPLICAS - 1)) * out.grid_stride;
+                atomicAdd(grid + rminy * gw + rminx, 1);
+                atomicAdd(grid + rminy * gw + rmaxx, -1);
+                atomicAdd(grid + rmaxy * gw + rminx, -1);
+                atomicAdd(grid + rmaxy * gw + rmaxx, 1);
+            }
+            const float L2E = 1.4426950408889634f;
+            const float BIG = 3.0e38f;  // every pixel of a touched tile evaluates the splat
+            out.rec0[g] = make_float4(pix, piy, BIG, BIG);
+            out.rec1[g] = make_float4(conic0 * (-0.5f * L2E), conic1 * (-L2E), conic2 * (-0.5f * L2E), opac);
+            out.rec2[g] = make_float4(c0, c1, c2, 1.f);  // renderCUDA always tests power > 0
+        }
+        out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
+        out.trect[g] = trect;
+        if (DEBUG) {
+            float4* d = reinterpret_cast<float4*>(out.dbg_vsout + 16 * (size_t)g);
+            d[0] = make_float4(vs[0], vs[1], vs[2], vs[3]);
+            d[1] = make_float4(vs[4], vs[5], vs[6], vs[7]);
+            d[2] = make_float4(vs[8], vs[9], vs[10], vs[11]);
+            d[3] = make_float4(vs[12], vs[13], 0.f, 0.f);
+            int4* e = reinterpret_cast<int4*>(out.dbg_setup + 8 * (size_t)g);
+            e[0] = make_int4(__float_as_int(ok ? pix : 0.f), __float_as_int(ok ? piy : 0.f),
+                             __float_as_int(ok ? depth : 0.f), ok ? 1 : 0);
+            e[1] = ok ? make_int4(rminx, rmaxx - 1, rminy, rmaxy - 1) : make_int4(0, -1, 0, -1);
+        }
+    }
+    const unsigned b = __ballot_sync(0xffffffffu, ok);
+    if ((threadIdx.x & 31) == 0 && b) atomicAdd(&s_visible, __popc(b));
+    __syncthreads();
+    if (threadIdx.x == 0 && s_visible) atomicAdd(&counters->n_visible, s_visible);
+}
+
 __global__ void k_set_params(FrameParams* dst, FrameParams fp, FrameCounters* counters) {
     if (threadIdx.x == 0) {
         *dst = fp;
@@ -386,6 +578,14 @@ void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers o
         if (dbg) k_preprocess<0, true><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
         else k_preprocess<0, false><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
     }
+}
+
+void launch_preprocess_official(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
+                                long long n, int sh_dim, cudaStream_t s) {
+    if (n <= 0) return;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    if (out.dbg_vsout) k_preprocess_official<true><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+    else k_preprocess_official<false><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
 }
 
 void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s, int negate) {

@@ -60,7 +60,7 @@ class B200Renderer(GaussianRenderBase):
     framebuffer.  ``read_pixels_rgb8`` / ``read_pixels_r32f`` stand in for the viewer's glReadPixels
     calls (main.py:852, 870)."""
 
-    def __init__(self, w, h, shaderpath=None, device=0, keys64=False):
+    def __init__(self, w, h, shaderpath=None, device=0, keys64=False, official_compat=False):
         super().__init__()
         import torch  # device memory + streams only
 
@@ -76,6 +76,9 @@ class B200Renderer(GaussianRenderBase):
         self.render_mod = 3
         self.is_depth_image = 0
         self.keys64 = bool(keys64)
+        # True: the semantics of the viewer's CUDA backend (renderer_cuda.py, diff_gaussian_rasterization forward)
+        # instead of the OpenGL shaders' — see GSR_FLAG_OFFICIAL in include/gsr.h
+        self.official_compat = bool(official_compat)
         self.auto_sort = True
         self.debug = False
         self.target_unorm = None  # None: unorm (clamped) target except in render_mod -1 (R32F FBO, main.py:866-870)
@@ -253,7 +256,7 @@ class B200Renderer(GaussianRenderBase):
                                             _fptr(self._campos), self._hff[0], self._hff[1], self._hff[2]))
         unorm = (self.render_mod != -1) if self.target_unorm is None else bool(self.target_unorm)
         flags = (_gsr.GSR_FLAG_CLAMP_UNORM if unorm else 0) | (_gsr.GSR_FLAG_KEYS64 if self.keys64 else 0) | \
-                (_gsr.GSR_FLAG_DEBUG if self.debug else 0)
+                (_gsr.GSR_FLAG_DEBUG if self.debug else 0) | (_gsr.GSR_FLAG_OFFICIAL if self.official_compat else 0)
         _gsr.check(self._lib.gsr_set_params(self._h, self.scale_modifier, self.render_mod, flags))
 
     def _stream(self):

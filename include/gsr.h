@@ -41,6 +41,14 @@ typedef enum {
 #define GSR_FLAG_CLAMP_UNORM 1u /* clamp source colour to [0,1] (RGB8 target semantics, main.py:852); off = float target (R32F, main.py:870) */
 #define GSR_FLAG_KEYS64 2u      /* sort duplicated 64-bit (tile<<32|depth) keys in one radix sort instead of the two-level depth-then-tile sort; identical result */
 #define GSR_FLAG_DEBUG 4u       /* keep per-stage intermediates for gsr_debug_fetch */
+#define GSR_FLAG_OFFICIAL 8u    /* CUDARenderer semantics (renderer_cuda.py:181-228): the forward pass of the out-of-tree,
+                                 * unpinned diff_gaussian_rasterization package restated from its published source —
+                                 * cull view z <= 0.2, radius ceil(3 sqrt(lambda_max)) tile squares, integer pixel
+                                 * coordinates, colour clamped at 0 from below, full SH degree (render_mod ignored),
+                                 * stop before T (1 - alpha) < 1e-4, alpha channel 1.  gsr_set_camera takes the same GL
+                                 * matrices; the z-forward view and P * view are derived like update_camera_pose does.
+                                 * With GSR_FLAG_DEBUG: VSOUT = visible, p_proj[3], radius x2, conic[3], color[3], opacity,
+                                 * depth; SETUP = pixel x, y, depth, ok, tile rect (inclusive, rows top-down). */
 
 /* gsr_debug_fetch selectors (GSR_FLAG_DEBUG must be set before the frame is rendered) */
 #define GSR_DBG_VSOUT 0      /* N x 16 f32: visible, ndc[3], half[2], conic[3], color[3], alpha, depth, pad[2] (layout of GsoVsOut) */

@@ -529,3 +529,163 @@ int gso_num_threads(void) {
     return 1;
 #endif
 }
+
+/* ---- official-rasterizer semantics (GSR_FLAG_OFFICIAL) -------------------------------------------------
+ * PARITY UNPINNED.  The viewer's CUDA backend (/root/reference/renderer_cuda.py:205-228) calls
+ * diff_gaussian_rasterization, which is not in the reference tree, has no pinned version (README.md:29) and
+ * cannot be installed offline.  This restates its published forward pass (graphdeco-inria/
+ * diff-gaussian-rasterization, cuda_rasterizer/forward.cu + auxiliary.h, the revision whose Python call
+ * returns (color, radii) as renderer_cuda.py:215 expects): preprocessCUDA, computeCov3D, computeCov2D,
+ * computeColorFromSH, getRect, the (tile << 32 | depth) key order and renderCUDA, anchored on the call site's
+ * settings (renderer_cuda.py:104-117: bg 0, prefiltered False, sh_degree sqrt(K)-1) and matrices (:181-203).
+ * cam->view = the z-forward view (GL view with rows 0 and 2 negated), cam->proj = P_gl * that view.
+ * Conventions as elsewhere in this file: binary32, no FMA contraction, left-to-right sums. */
+static int official_one(const float* p3, const float* rot4, const float* scale3, float opacity, const float* sh,
+                        const GsoCamera* cam, int W, int H, GsoVsOut* o, GsoSetup* s) {
+    memset(o, 0, sizeof(*o));
+    memset(s, 0, sizeof(*s));
+    s->imin = 0; s->imax = -1; s->jmin = 0; s->jmax = -1;
+    const int tiles_x = (W + 15) / 16, tiles_y = (H + 15) / 16;
+    const float g_pos[4] = {p3[0], p3[1], p3[2], 1.f};
+    float pv[4], ph[4];
+    mat4_mul_vec4(cam->view, g_pos, pv);
+    if (!(pv[2] > 0.2f)) return 0; /* in_frustum */
+    mat4_mul_vec4(cam->proj, g_pos, ph);
+    const float p_w = 1.0f / (ph[3] + 0.0000001f);
+    const float pp[3] = {ph[0] * p_w, ph[1] * p_w, ph[2] * p_w};
+    float sc[3];
+    for (int k = 0; k < 3; ++k) sc[k] = cam->scale_modifier * scale3[k];
+    m3 cov3d = compute_cov3d(sc, rot4);
+    const float focal_x = (float)W / (2.0f * cam->hfovxy_focal[0]);
+    const float focal_y = (float)H / (2.0f * cam->hfovxy_focal[1]);
+    float cov[3];
+    compute_cov2d(pv, focal_x, focal_y, cam->hfovxy_focal[0], cam->hfovxy_focal[1], &cov3d, cam->view, cov);
+    const float det = (cov[0] * cov[2] - cov[1] * cov[1]);
+    if (det == 0.0f) return 0;
+    const float det_inv = 1.f / det;
+    const float conic[3] = {cov[2] * det_inv, -cov[1] * det_inv, cov[0] * det_inv};
+    const float mid = 0.5f * (cov[0] + cov[2]);
+    const float disc = sqrtf(gl_max(0.1f, mid * mid - det));
+    const float lambda1 = mid + disc, lambda2 = mid - disc;
+    const float radius = ceilf(3.f * sqrtf(gl_max(lambda1, lambda2)));
+    const float pix = (float)((((double)pp[0] + 1.0) * (double)W - 1.0) * 0.5); /* ndc2Pix, double literals */
+    const float piy = (float)((((double)pp[1] + 1.0) * (double)H - 1.0) * 0.5);
+    if (!isfinite(pix) || !isfinite(piy) || !isfinite(radius)) return 0;
+    const float lim = 1.0e9f;
+    const float ax = gl_min(lim, gl_max(-lim, (pix - radius) / 16.f));
+    const float bx = gl_min(lim, gl_max(-lim, (pix + radius + 15.f) / 16.f));
+    const float ay = gl_min(lim, gl_max(-lim, (piy - radius) / 16.f));
+    const float by = gl_min(lim, gl_max(-lim, (piy + radius + 15.f) / 16.f));
+    int rminx = (int)ax, rmaxx = (int)bx, rminy = (int)ay, rmaxy = (int)by;
+    rminx = rminx < 0 ? 0 : (rminx > tiles_x ? tiles_x : rminx); rmaxx = rmaxx < 0 ? 0 : (rmaxx > tiles_x ? tiles_x : rmaxx);
+    rminy = rminy < 0 ? 0 : (rminy > tiles_y ? tiles_y : rminy); rmaxy = rmaxy < 0 ? 0 : (rmaxy > tiles_y ? tiles_y : rmaxy);
+    if ((rmaxx - rminx) * (rmaxy - rminy) == 0) return 0;
+    float dir[3] = {p3[0] - cam->cam_pos[0], p3[1] - cam->cam_pos[1], p3[2] - cam->cam_pos[2]};
+    const float len = sqrtf((dir[0] * dir[0] + dir[1] * dir[1]) + dir[2] * dir[2]);
+    dir[0] = dir[0] / len; dir[1] = dir[1] / len; dir[2] = dir[2] / len;
+    const int sh_dim = cam->sh_dim;
+    float c[3];
+#define SHV(k, ch) sh[(k) * 3 + (ch)]
+    for (int ch = 0; ch < 3; ++ch) c[ch] = SH_C0 * SHV(0, ch);
+    if (sh_dim > 3) {
+        const float x = dir[0], y = dir[1], z = dir[2];
+        for (int ch = 0; ch < 3; ++ch)
+            c[ch] = c[ch] - SH_C1 * y * SHV(1, ch) + SH_C1 * z * SHV(2, ch) - SH_C1 * x * SHV(3, ch);
+        if (sh_dim > 12) {
+            const float xx = x * x, yy = y * y, zz = z * z;
+            const float xy = x * y, yz = y * z, xz = x * z;
+            for (int ch = 0; ch < 3; ++ch)
+                c[ch] = c[ch] + SH_C2_0 * xy * SHV(4, ch) + SH_C2_1 * yz * SHV(5, ch) +
+                        SH_C2_2 * (2.0f * zz - xx - yy) * SHV(6, ch) + SH_C2_3 * xz * SHV(7, ch) +
+                        SH_C2_4 * (xx - yy) * SHV(8, ch);
+            if (sh_dim > 27) {
+                for (int ch = 0; ch < 3; ++ch)
+                    c[ch] = c[ch] + SH_C3_0 * y * (3.0f * xx - yy) * SHV(9, ch) + SH_C3_1 * xy * z * SHV(10, ch) +
+                            SH_C3_2 * y * (4.0f * zz - xx - yy) * SHV(11, ch) +
+                            SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SHV(12, ch) +
+                            SH_C3_4 * x * (4.0f * zz - xx - yy) * SHV(13, ch) + SH_C3_5 * z * (xx - yy) * SHV(14, ch) +
+                            SH_C3_6 * x * (xx - 3.0f * yy) * SHV(15, ch);
+            }
+        }
+    }
+#undef SHV
+    o->visible = 1.f;
+    o->ndc[0] = pp[0]; o->ndc[1] = pp[1]; o->ndc[2] = pp[2];
+    o->half[0] = radius; o->half[1] = radius;
+    o->conic[0] = conic[0]; o->conic[1] = conic[1]; o->conic[2] = conic[2];
+    for (int ch = 0; ch < 3; ++ch) o->color[ch] = gl_max(c[ch] + 0.5f, 0.f);
+    o->alpha = opacity;
+    o->depth = pv[2];
+    s->cx = pix; s->cy = piy; s->depth = pv[2]; s->ok = 1;
+    s->imin = rminx; s->imax = rmaxx - 1; s->jmin = rminy; s->jmax = rmaxy - 1;
+    return 1;
+}
+
+int gso_official_preprocess(const float* xyz, const float* rot, const float* scale, const float* opacity, const float* sh,
+                            int n, const GsoCamera* cam, int W, int H, GsoVsOut* vs, GsoSetup* setup) {
+#pragma omp parallel for schedule(static)
+    for (int g = 0; g < n; ++g)
+        official_one(xyz + 3 * (size_t)g, rot + 4 * (size_t)g, scale + 3 * (size_t)g, opacity[g],
+                     sh + (size_t)cam->sh_dim * (size_t)g, cam, W, H, &vs[g], &setup[g]);
+    return 0;
+}
+
+/* renderCUDA for every tile; out_rgba: H*W*4 floats, row 0 = top, alpha = 1 (renderer_cuda.py:227).
+ * fragile: optional H*W bytes, 1 where a threshold decision (alpha < 1/255, power > 0) was within FRAG_EPS of
+ * flipping.  Returns the number of Gaussians that passed preprocess. */
+int gso_official_render(const float* xyz, const float* rot, const float* scale, const float* opacity, const float* sh,
+                        int n, const GsoCamera* cam, int W, int H, float* out_rgba, unsigned char* fragile) {
+    GsoVsOut* vs = (GsoVsOut*)malloc(sizeof(GsoVsOut) * (size_t)(n ? n : 1));
+    GsoSetup* st = (GsoSetup*)malloc(sizeof(GsoSetup) * (size_t)(n ? n : 1));
+    int* order = (int*)malloc(sizeof(int) * (size_t)(n ? n : 1));
+    gso_official_preprocess(xyz, rot, scale, opacity, sh, n, cam, W, H, vs, st);
+    const int m = gso_visible_order(st, n, order); /* stable by (depth bits, index) */
+    const int tiles_x = (W + 15) / 16, tiles_y = (H + 15) / 16, nt = tiles_x * tiles_y;
+    size_t* start = (size_t*)calloc((size_t)nt + 1, sizeof(size_t));
+    for (int k = 0; k < m; ++k) {
+        const GsoSetup* s = &st[order[k]];
+        for (int ty = s->jmin; ty <= s->jmax; ++ty)
+            for (int tx = s->imin; tx <= s->imax; ++tx) start[ty * tiles_x + tx + 1]++;
+    }
+    for (int t = 0; t < nt; ++t) start[t + 1] += start[t];
+    int* list = (int*)malloc(sizeof(int) * (start[nt] ? start[nt] : 1));
+    size_t* fill = (size_t*)malloc(sizeof(size_t) * (size_t)nt);
+    memcpy(fill, start, sizeof(size_t) * (size_t)nt);
+    for (int k = 0; k < m; ++k) {
+        const GsoSetup* s = &st[order[k]];
+        for (int ty = s->jmin; ty <= s->jmax; ++ty)
+            for (int tx = s->imin; tx <= s->imax; ++tx) list[fill[ty * tiles_x + tx]++] = order[k];
+    }
+    if (fragile) memset(fragile, 0, (size_t)W * (size_t)H);
+    const float FE = 2e-5f;
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int t = 0; t < nt; ++t) {
+        const int tx = t % tiles_x, ty = t / tiles_x;
+        for (int j = ty * 16; j < ty * 16 + 16 && j < H; ++j)
+            for (int i = tx * 16; i < tx * 16 + 16 && i < W; ++i) {
+                float T = 1.f, C[3] = {0.f, 0.f, 0.f};
+                unsigned char fr = 0;
+                for (size_t k = start[t]; k < start[t + 1]; ++k) {
+                    const int g = list[k];
+                    const float dx = st[g].cx - (float)i, dy = st[g].cy - (float)j;
+                    const float* con = vs[g].conic;
+                    const float power = -0.5f * (con[0] * dx * dx + con[2] * dy * dy) - con[1] * dx * dy;
+                    if (fabsf(power) <= FE) fr = 1;
+                    if (power > 0.f) continue;
+                    const float alpha = gl_min(0.99f, vs[g].alpha * expf(power));
+                    if (fabsf(alpha - 1.f / 255.f) <= FE * (1.f / 255.f) * 4.f) fr = 1;
+                    if (alpha < 1.f / 255.f) continue;
+                    const float test_T = T * (1.f - alpha);
+                    /* a flipped stop decision moves the pixel by less than 1e-4: not fragile */
+                    if (test_T < 0.0001f) break;
+                    for (int ch = 0; ch < 3; ++ch) C[ch] += vs[g].color[ch] * alpha * T;
+                    T = test_T;
+                }
+                float* o = out_rgba + 4 * ((size_t)j * (size_t)W + (size_t)i);
+                o[0] = C[0]; o[1] = C[1]; o[2] = C[2]; o[3] = 1.f; /* bg = 0: C + T * bg */
+                if (fragile) fragile[(size_t)j * (size_t)W + (size_t)i] = fr;
+            }
+    }
+    free(vs); free(st); free(order); free(start); free(list); free(fill);
+    return m;
+}

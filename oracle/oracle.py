@@ -203,3 +203,48 @@ def ref_render(gau, order, cam: Camera, W: int, H: int, clamp_unorm: bool = True
     L.gsref_render(_p(flat), C.c_int(n), _p(order, C.c_int), C.byref(cam), C.c_int(W), C.c_int(H),
                    C.c_int(1 if clamp_unorm else 0), _p(img))
     return img
+
+
+# ---- official-rasterizer semantics (parity unpinned; see the header of that section in gs_oracle.c) ---------
+def official_matrices(view, proj):
+    """What CUDARenderer.update_camera_pose builds (/root/reference/renderer_cuda.py:181-194): the view with rows
+    0 and 2 negated and P @ view, in binary32 with left-to-right sums (the arithmetic of gsr_api.cu)."""
+    vo = np.array(view, dtype=np.float32, copy=True).reshape(4, 4)
+    vo[[0, 2], :] = -vo[[0, 2], :]
+    P = np.asarray(proj, dtype=np.float32).reshape(4, 4)
+    po = np.zeros((4, 4), dtype=np.float32)
+    for r in range(4):
+        for c in range(4):
+            acc = np.float32(P[r, 0] * vo[0, c])
+            for k in range(1, 4):
+                acc = np.float32(acc + np.float32(P[r, k] * vo[k, c]))
+            po[r, c] = acc
+    return vo, po
+
+
+def official_camera(view, proj, hfovxy_focal, cam_pos, scale_modifier=1.0, sh_dim=48) -> Camera:
+    vo, po = official_matrices(view, proj)
+    return make_camera(vo, po, hfovxy_focal, cam_pos, scale_modifier, 3, sh_dim)
+
+
+def official_preprocess(gau, cam: Camera, W: int, H: int):
+    n = len(gau)
+    xyz, rot, scale, op, sh = _f32(gau.xyz), _f32(gau.rot), _f32(gau.scale), _f32(gau.opacity), _f32(gau.sh)
+    vs = np.zeros(n, dtype=VS_DTYPE)
+    st = np.zeros(n, dtype=SETUP_DTYPE)
+    oracle_lib().gso_official_preprocess(_p(xyz), _p(rot), _p(scale), _p(op), _p(sh), C.c_int(n), C.byref(cam),
+                                         C.c_int(W), C.c_int(H), vs.ctypes.data_as(C.c_void_p),
+                                         st.ctypes.data_as(C.c_void_p))
+    return vs, st
+
+
+def official_render(gau, cam: Camera, W: int, H: int, want_fragile: bool = False):
+    """-> (rgba (H,W,4) f32 top-down with alpha 1, fragile (H,W) u8 or None, n_drawn)"""
+    n = len(gau)
+    xyz, rot, scale, op, sh = _f32(gau.xyz), _f32(gau.rot), _f32(gau.scale), _f32(gau.opacity), _f32(gau.sh)
+    img = np.zeros((H, W, 4), dtype=np.float32)
+    frag = np.zeros((H, W), dtype=np.uint8) if want_fragile else None
+    m = oracle_lib().gso_official_render(_p(xyz), _p(rot), _p(scale), _p(op), _p(sh), C.c_int(n), C.byref(cam),
+                                         C.c_int(W), C.c_int(H), _p(img),
+                                         frag.ctypes.data_as(C.c_void_p) if want_fragile else None)
+    return img, frag, m
