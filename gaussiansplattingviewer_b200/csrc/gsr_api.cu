@@ -963,6 +963,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_BLEND_SHAPE8: set_blend_shape8(value); return 0;
         case GSR_TUNE_BLEND_SKIP: set_blend_skip(value); return 0;
         case GSR_TUNE_SORT_PREFETCH: set_sort_prefetch(value); return 0;
+        case GSR_TUNE_SORT_MATCH_MIX: set_sort_mix(value); return 0;
         case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;
         default: return fail(GSR_EINVAL, "unknown tuning key");
     }
