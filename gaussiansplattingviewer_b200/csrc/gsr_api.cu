@@ -80,6 +80,9 @@ struct gsr_renderer {
     int order_buf = -1;                      // d_gid[] buffer holding a shared depth order (stereo capture, frozen order)
     bool order_frozen = false;               // gsr_freeze_order: frames draw in the stored order
     cudaStream_t copy_stream = nullptr;
+    // frame-internal fork: scratch clears and the single-CTA k_tile_scan run beside preprocess / the depth sort
+    cudaStream_t aux_stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_pre = nullptr, ev_cleared = nullptr, ev_scan = nullptr;
     cudaEvent_t ev_packed[2] = {}, ev_copied[2] = {};
     bool slot_busy[2] = {false, false};
     unsigned async_idx = 0;
@@ -104,6 +107,8 @@ struct gsr_renderer {
 };
 
 namespace {
+
+int g_frame_fork = 1;  // gsr_tune(GSR_TUNE_FRAME_FORK): 0 = every frame runs on one stream
 
 int free_gaussian_buffers(gsr_t* h) {
     dfree(h->d_xyz); dfree(h->d_rot); dfree(h->d_scale_op); dfree(h->d_sh);
@@ -252,14 +257,24 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     sp.grid_w = h->grid_w;
     sp.grid_stride = h->grid_w * (h->tiles_y + 1);
 
+    // Untimed frames fork: the scratch clears run beside the preprocess kernel and the single-CTA k_tile_scan
+    // beside the depth sort, on the handle's auxiliary stream (joined by events; no host synchronisation).
+    // Timed frames stay on one stream so that the per-stage events bracket exactly one stage each.
+    const bool fork = !timed && !keys64 && g_frame_fork;
+    cudaStream_t sa = fork ? h->aux_stream : s;
+    const long long sort_upper = cap;
     if (timed) cudaEventRecord(h->ev[0], s);
+    if (fork) {
+        CK(cudaEventRecord(h->ev_start, s));
+        CK(cudaStreamWaitEvent(sa, h->ev_start, 0));
+    }
     launch_set_params(h->d_fp, fp, h->d_counters, s);
     CK(cudaMemsetAsync(h->d_tile_grid, 0, sizeof(int) * (size_t)sp.grid_stride * GSR_GRID_REPLICAS, s));
     if (official) launch_preprocess_official(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     else launch_preprocess(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     h->launches += 2;
     if (timed) cudaEventRecord(h->ev[1], s);
-    CK(cudaMemsetAsync(h->d_chain, 0, h->chain_bytes, s));
+    CK(cudaMemsetAsync(h->d_chain, 0, h->chain_bytes, sa));
     uint32_t* chain_ticket = reinterpret_cast<uint32_t*>(h->d_chain + (h->chain_bytes / 8 - 1));
     uint32_t* big_count = reinterpret_cast<uint32_t*>(h->d_chain + (h->chain_bytes / 8 - 2));
     const uint32_t* n_sort = &h->d_counters->n_sort;
@@ -267,7 +282,20 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     if (!keys64) {
         // depth sort of the N Gaussians (culled ones carry key 0xFFFFFFFF and sort to the end)
         // (the two mantissa bytes of a depth key are spread over their bins, the exponent bytes are not)
-        SortOptions so_n = {0, false, false, 0x3u};
+        SortOptions so_n = {0, false, false, 0x3u, fork};
+        SortOptions so = {scan_hist ? bits0 : 0, scan_hist, true, 0u, fork};
+        if (fork) {
+            if (order_mode != 2) sort_scratch_clear<uint32_t>(&h->ss_n, N, false, sa);
+            sort_scratch_clear<uint32_t>(&h->ss_i, sort_upper, scan_hist, sa);
+            CK(cudaEventRecord(h->ev_cleared, sa));
+            CK(cudaEventRecord(h->ev_pre, s));
+            CK(cudaStreamWaitEvent(sa, h->ev_pre, 0));
+            launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges,
+                             h->ss_i.hist, h->d_counters, sa);
+            h->launches += 1;
+            CK(cudaEventRecord(h->ev_scan, sa));
+            CK(cudaStreamWaitEvent(s, h->ev_cleared, 0));
+        }
         int r0 = h->order_buf;
         if (order_mode != 2) {
             r0 = radix_sort_pairs<uint32_t>(h->sp.depth_key, h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1],
@@ -277,15 +305,18 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
         const uint32_t* sorted_gid = h->d_gid[r0];
         if (timed) cudaEventRecord(h->ev[2], s);
         // counts -> ranges, D, overflow flag, digit histograms of the tile sort
-        launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges, h->ss_i.hist,
-                         h->d_counters, s);
-        h->launches += 1;
+        if (fork) {
+            CK(cudaStreamWaitEvent(s, h->ev_scan, 0));
+        } else {
+            launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges,
+                             h->ss_i.hist, h->d_counters, s);
+            h->launches += 1;
+        }
         if (timed) cudaEventRecord(h->ev[3], s);
         launch_duplicate_sorted(h->d_fp, sorted_gid, sp, h->d_counters, reinterpret_cast<uint32_t*>(h->d_chain),
                                 chain_ticket, (uint32_t*)h->d_ikeys[0], h->d_ivals[0], h->d_big, big_count, N, cap, s);
         h->launches += 2;
         if (timed) cudaEventRecord(h->ev[4], s);
-        SortOptions so = {scan_hist ? bits0 : 0, scan_hist, true, 0u};
         res = radix_sort_pairs<uint32_t>((uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[0], (uint32_t*)h->d_ikeys[1],
                                          h->d_ivals[0], h->d_ivals[1], false, 0, n_sort, cap, 0, tbits, &h->ss_i, s,
                                          &h->launches, &so);
@@ -372,6 +403,9 @@ int gsr_create(int device, gsr_t** out) {
     memset(h->h_counters, 0, sizeof(FrameCounters));
     for (auto& ev : h->ev) CK(cudaEventCreate(&ev));
     CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
+    for (cudaEvent_t* e : {&h->ev_start, &h->ev_pre, &h->ev_cleared, &h->ev_scan})
+        CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     for (int i = 0; i < 2; ++i) {
         CK(cudaEventCreateWithFlags(&h->ev_packed[i], cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming));
@@ -392,6 +426,8 @@ int gsr_destroy(gsr_t* h) {
     dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_rgb8b); dfree(h->d_r32);
     dfree(h->d_cap[0]); dfree(h->d_cap[1]);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+    if (h->aux_stream) cudaStreamDestroy(h->aux_stream);
+    for (cudaEvent_t e : {h->ev_start, h->ev_pre, h->ev_cleared, h->ev_scan}) if (e) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) { if (h->ev_packed[i]) cudaEventDestroy(h->ev_packed[i]); if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]); }
     dfree(h->d_fp); dfree(h->d_counters); dfree(h->d_sortp);
     if (h->h_counters) cudaFreeHost(h->h_counters);
@@ -964,6 +1000,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_BLEND_SKIP: set_blend_skip(value); return 0;
         case GSR_TUNE_SORT_PREFETCH: set_sort_prefetch(value); return 0;
         case GSR_TUNE_SORT_MATCH_MIX: set_sort_mix(value); return 0;
+        case GSR_TUNE_FRAME_FORK: g_frame_fork = value ? 1 : 0; return 0;
         case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;
         default: return fail(GSR_EINVAL, "unknown tuning key");
     }

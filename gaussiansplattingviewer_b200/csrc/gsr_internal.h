@@ -90,7 +90,11 @@ struct SortOptions {
     bool hist_ready;
     bool vals_only_last;
     unsigned hist_direct_mask;  // passes whose digits are spread over their bins: count them without the warp match
+    bool scratch_cleared;       // the caller already ran sort_scratch_clear (e.g. on another stream)
 };
+// the clears radix_sort_pairs starts with (histograms + tickets, or tickets + first look-back rows when hist_ready)
+template <typename KeyT>
+void sort_scratch_clear(SortScratch* scratch, long long upper, bool hist_ready, cudaStream_t stream);
 template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
                      long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,

@@ -544,6 +544,23 @@ int rs2_ctas_per_sm() {  // 0 = the variant cannot run here
 }
 
 template <typename KeyT>
+void sort_scratch_clear(SortScratch* scratch, long long upper, bool hist_ready, cudaStream_t stream) {
+    if (upper <= 0) return;
+    if (hist_ready) {
+        // the digit histograms come from the caller (k_tile_scan): clear the tickets and the look-back rows of
+        // the first pass only
+        const int TILE = RS_THREADS * (g_rs_small ? RsCfg<KeyT>::SMALL : RsCfg<KeyT>::LARGE);
+        const long long tiles_upper = (upper + TILE - 1) / TILE;
+        cudaMemsetAsync(scratch->tickets, 0, 64 * sizeof(uint32_t), stream);
+        cudaMemsetAsync(scratch->status[0], 0, (size_t)tiles_upper * 256 * sizeof(uint32_t), stream);
+    } else {
+        cudaMemsetAsync(scratch->hist, 0, scratch->zero_bytes, stream);  // histograms + tickets; k_rs_hist clears the rows
+    }
+}
+template void sort_scratch_clear<uint32_t>(SortScratch*, long long, bool, cudaStream_t);
+template void sort_scratch_clear<uint64_t>(SortScratch*, long long, bool, cudaStream_t);
+
+template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
                      long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
                      SortScratch* scratch, cudaStream_t stream, long long* launch_count, const SortOptions* opt) {
@@ -568,13 +585,8 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
     const int TILE = RS_THREADS * (small ? RsCfg<KeyT>::SMALL : RsCfg<KeyT>::LARGE);
     const long long tiles_upper = (upper + TILE - 1) / TILE;
     const int sms = num_sms();
-    if (hist_ready) {
-        // the digit histograms were produced by the caller (k_tile_scan): clear the tickets and the
-        // look-back rows of the first pass only
-        cudaMemsetAsync(scratch->tickets, 0, 64 * sizeof(uint32_t), stream);
-        cudaMemsetAsync(scratch->status[0], 0, (size_t)tiles_upper * 256 * sizeof(uint32_t), stream);
-    } else {
-        cudaMemsetAsync(scratch->hist, 0, scratch->zero_bytes, stream);
+    if (!(opt && opt->scratch_cleared)) sort_scratch_clear<KeyT>(scratch, upper, hist_ready, stream);
+    if (!hist_ready) {
         long long g = (upper + RS_THREADS * 8 - 1) / (RS_THREADS * 8);
         if (g > sms * 8) g = sms * 8;
         if (g < 1) g = 1;
