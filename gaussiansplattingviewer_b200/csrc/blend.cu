@@ -51,9 +51,9 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                                                      unsigned long long* __restrict__ pair_counts) {
     constexpr int THREADS = 256 / PPT;
     constexpr int PER_THREAD = (BL_BATCH + THREADS - 1) / THREADS;  // records staged per thread per batch
-    __shared__ __align__(16) float4 s0[2][BL_BATCH];
-    __shared__ __align__(16) float4 s1[2][BL_BATCH];
-    __shared__ __align__(16) float4 s2[2][BL_BATCH];
+    // one record = three consecutive float4 (48 B): the three shared-memory reads of a splat are constant
+    // offsets from one running pointer
+    __shared__ __align__(16) float4 s_rec[2][BL_BATCH][3];
     const int W = fp->W, H = fp->H;
     const int tile = blockIdx.y * gridDim.x + blockIdx.x;
     // pixel block of a warp: SHAPE8 = 8 columns x (4 * PPT) rows (compact: better quad / termination
@@ -104,9 +104,9 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
             const int slot = threadIdx.x + i * THREADS;
             const uint32_t g = gid_next[i];
             if (g != 0xFFFFFFFFu) {
-                cp_async16(&s0[buf][slot], sp.rec0 + g);
-                cp_async16(&s1[buf][slot], sp.rec1 + g);
-                cp_async16(&s2[buf][slot], sp.rec2 + g);
+                cp_async16(&s_rec[buf][slot][0], sp.rec0 + g);
+                cp_async16(&s_rec[buf][slot][1], sp.rec1 + g);
+                cp_async16(&s_rec[buf][slot][2], sp.rec2 + g);
             }
         }
         cp_async_commit();
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
 #pragma unroll
         for (int i = 0; i < PER_THREAD; ++i) {
             const int slot = threadIdx.x + i * THREADS;
-            if (slot < cnt) flagged = flagged || (s2[buf][slot].w != 0.f);
+            if (slot < cnt) flagged = flagged || (s_rec[buf][slot][2].w != 0.f);
         }
         const bool check_power = __syncthreads_or(flagged ? 1 : 0) != 0;
         bool live = false;
@@ -144,7 +144,8 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
             constexpr bool CHECK_POWER = decltype(tag)::value;
 #pragma unroll 2
             for (int j = 0; j < cnt; ++j) {
-                const float4 a = s0[buf][j];  // cx, cy, hx, hy
+                const float4* rec = &s_rec[buf][j][0];
+                const float4 a = rec[0];  // cx, cy, hx, hy
                 const float dx = pxf - a.x;
                 const bool inx = fabsf(dx) <= a.z;
                 float dy[PPT];
@@ -159,8 +160,8 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                 }
                 // no live pixel of this warp lies inside the quad: skip the splat for 3 instructions
                 if (SKIP && !__any_sync(0xffffffffu, any_in)) continue;
-                const float4 q = s1[buf][j];  // A', B', C' (pre-scaled conic), opacity
-                const float4 c = s2[buf][j];  // r, g, b, flag: conic not positive definite
+                const float4 q = rec[1];  // A', B', C' (pre-scaled conic), opacity
+                const float4 c = rec[2];  // r, g, b, flag: conic not positive definite
                 const float bdx = q.y * dx;
                 const float adx2 = q.x * dx * dx;
 #pragma unroll
@@ -187,7 +188,21 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                             T[k] = stop ? 0.f : (hit ? test_T : T[k]);
                         } else if (MODE == 0) {
                             if (COUNT) n_hit += valid ? 1u : 0u;
-                            const float w = valid ? alpha * T[k] : 0.f;
+                            float w;
+                            if (!COUNT && !CHECK_POWER) {
+                                // one compare that ANDs in the coverage predicate, one select (the compiler otherwise
+                                // selects twice): w = (in && !(alpha < 1/255)) ? alpha * T : 0
+                                asm("{\n\t"
+                                    ".reg .pred p, q;\n\t"
+                                    "setp.ne.u32 q, %2, 0;\n\t"
+                                    "setp.geu.and.f32 p, %1, 0f3B808081, q;\n\t"
+                                    "selp.f32 %0, %3, 0f00000000, p;\n\t"
+                                    "}"
+                                    : "=f"(w)
+                                    : "f"(alpha), "r"((unsigned)in[k]), "f"(alpha * T[k]));
+                            } else {
+                                w = valid ? alpha * T[k] : 0.f;
+                            }
                             cr[k] = fmaf(w, c.x, cr[k]); cg[k] = fmaf(w, c.y, cg[k]); cb[k] = fmaf(w, c.z, cb[k]);
                             T[k] -= w;
                         } else {  // flat / gaussian ball: alpha becomes 1 above 0.22, 0 below
