@@ -44,7 +44,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // kernel renderer_cuda.py:212-224 calls): pixel coordinates are integers, rows run top-down, every pixel of a
 // touched tile evaluates the splat (the record carries infinite half extents), `power > 0` is always tested, a
 // pixel stops BEFORE blending the splat that would take T * (1 - alpha) below 1e-4, and alpha is written as 1.
-template <int MODE, int PPT, bool COUNT, bool SHAPE8, bool SKIP>
+template <int MODE, int PPT, bool COUNT, bool SHAPE8, int SKIP>  // SKIP: 0 none, 1 warp vote per splat, 2 warp filter per batch
 __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
                                                      const uint32_t* __restrict__ inst_gid, SplatBuffers sp,
                                                      float* __restrict__ out_rgba, unsigned flags,
@@ -67,6 +67,23 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
     } else {
         lx = threadIdx.x & (GSR_TILE - 1);
         lyb = threadIdx.x / GSR_TILE;
+    }
+    // pixel-centre bounds of the warp's block, widened by 0.01 px (SKIP == 2)
+    float bx0, bx1, by0, by1;
+    {
+        const int warp = threadIdx.x >> 5;
+        int wx0, wy0, ww, wh;
+        if (SHAPE8) {
+            constexpr int WARPS_Y = GSR_TILE / (4 * PPT);
+            wx0 = (warp / WARPS_Y) * 8; wy0 = (warp % WARPS_Y) * 4 * PPT; ww = 8; wh = 4 * PPT;
+        } else {
+            wx0 = 0; wy0 = warp * 2 * PPT; ww = GSR_TILE; wh = 2 * PPT;
+        }
+        constexpr float C0 = (MODE == 5) ? 0.f : 0.5f;
+        bx0 = (float)(blockIdx.x * GSR_TILE + wx0) + C0 - 0.01f;
+        bx1 = (float)(blockIdx.x * GSR_TILE + wx0 + ww - 1) + C0 + 0.01f;
+        by0 = (float)(blockIdx.y * GSR_TILE + wy0) + C0 - 0.01f;
+        by1 = (float)(blockIdx.y * GSR_TILE + wy0 + wh - 1) + C0 + 0.01f;
     }
     const int px = blockIdx.x * GSR_TILE + lx;
     const int py0 = blockIdx.y * GSR_TILE + lyb * PPT;  // GL row, 0 = bottom
@@ -142,8 +159,7 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
         for (int k = 0; k < PPT; ++k) live = live || (T[k] >= 1e-4f);
         auto run_batch = [&](auto tag) {
             constexpr bool CHECK_POWER = decltype(tag)::value;
-#pragma unroll 2
-            for (int j = 0; j < cnt; ++j) {
+            auto splat = [&](int j) {
                 const float4* rec = &s_rec[buf][j][0];
                 const float4 a = rec[0];  // cx, cy, hx, hy
                 const float dx = pxf - a.x;
@@ -159,7 +175,7 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                     any_in = any_in || in[k];
                 }
                 // no live pixel of this warp lies inside the quad: skip the splat for 3 instructions
-                if (SKIP && !__any_sync(0xffffffffu, any_in)) continue;
+                if (SKIP == 1 && !__any_sync(0xffffffffu, any_in)) return;
                 const float4 q = rec[1];  // A', B', C' (pre-scaled conic), opacity
                 const float4 c = rec[2];  // r, g, b, flag: conic not positive definite
                 const float bdx = q.y * dx;
@@ -219,6 +235,41 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                         }
                     }
                 }
+            };
+            if (SKIP == 2) {
+                // Warp-level filter: each lane tests four records of the batch against the warp's pixel block
+                // (conservatively: splat box vs block box, 0.01 px of slack against rounding), the ballots give the
+                // hit list, and only hits run the per-pixel body.  A 16x16 tile's splat touches on average fewer
+                // than half of the four 8x8 warp blocks; testing them one by one cost 16 instructions per miss.
+                const int lane = threadIdx.x & 31;
+                constexpr int NW = BL_BATCH / 32;
+                uint32_t hits[NW];
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                    const int j = i * 32 + lane;
+                    const float4 a = s_rec[buf][j][0];
+                    const bool keep = (j < cnt) && (a.x + a.z >= bx0) && (a.x - a.z <= bx1) && (a.y + a.w >= by0) &&
+                                      (a.y - a.w <= by1);
+                    hits[i] = __ballot_sync(0xffffffffu, keep);
+                }
+#pragma unroll
+                for (int i = 0; i < NW; ++i) {
+                    uint32_t m = hits[i];
+                    if (m == 0u) continue;
+                    // pixels die as the batch goes on: re-check once per 32 records
+                    bool alive = false;
+#pragma unroll
+                    for (int k = 0; k < PPT; ++k) alive = alive || (T[k] >= 1e-4f);
+                    if (!__any_sync(0xffffffffu, alive)) break;
+                    while (m) {
+                        const int bit = __ffs(m) - 1;
+                        m &= m - 1u;
+                        splat(i * 32 + bit);
+                    }
+                }
+            } else {
+#pragma unroll 2
+                for (int j = 0; j < cnt; ++j) splat(j);
             }
         };
         if (__any_sync(0xffffffffu, live)) {
@@ -280,17 +331,18 @@ __global__ void k_pack_disp_u16(const float4* __restrict__ rgba, uint16_t* __res
 }
 
 // kernel-variant knobs (gsr_tune): pixels per thread, warp block shape, warp-level quad skip
-int g_blend_ppt = 2, g_blend_shape8 = 1, g_blend_skip = 1;
+int g_blend_ppt = 2, g_blend_shape8 = 1, g_blend_skip = 2;
 
 }  // namespace
 
 void set_blend_ppt(int v) { if (v == 1 || v == 2 || v == 4) g_blend_ppt = v; }
 void set_blend_shape8(int v) { g_blend_shape8 = v ? 1 : 0; }
-void set_blend_skip(int v) { g_blend_skip = v ? 1 : 0; }
+void set_blend_skip(int v) { g_blend_skip = (v == 2) ? 2 : (v ? 1 : 0); }
 
 // default configuration (every mode, and the counting variant)
 constexpr int BL_PPT = 2;
-constexpr bool BL_SHAPE8 = true, BL_SKIP = true;
+constexpr bool BL_SHAPE8 = true;
+constexpr int BL_SKIP = 2;
 
 template <bool COUNT>
 static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
@@ -299,25 +351,22 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
     const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
     constexpr int TH = 256 / BL_PPT;
 #define BL_ARGS fp, ranges, inst_gid, sp, out_rgba, flags, pc
-    if (flags & GSR_FLAG_OFFICIAL_BIT) k_blend<5, BL_PPT, COUNT, BL_SHAPE8, false><<<grid, TH, 0, s>>>(BL_ARGS);
+    if (flags & GSR_FLAG_OFFICIAL_BIT) k_blend<5, BL_PPT, COUNT, BL_SHAPE8, 0><<<grid, TH, 0, s>>>(BL_ARGS);
     else if (render_mod == -2) k_blend<2, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
     else if (render_mod == -3) k_blend<3, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
     else if (render_mod == -4) k_blend<4, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
     else if (COUNT) k_blend<0, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
     else {
         // measurement variants of the main mode
-        const int v = (g_blend_ppt == 4 ? 4 : (g_blend_ppt == 1 ? 8 : 0)) | (g_blend_shape8 ? 2 : 0) | (g_blend_skip ? 1 : 0);
-        switch (v) {
-            case 0: k_blend<0, 2, false, false, false><<<grid, 128, 0, s>>>(BL_ARGS); break;
-            case 1: k_blend<0, 2, false, false, true><<<grid, 128, 0, s>>>(BL_ARGS); break;
-            case 2: k_blend<0, 2, false, true, false><<<grid, 128, 0, s>>>(BL_ARGS); break;
-            case 3: k_blend<0, 2, false, true, true><<<grid, 128, 0, s>>>(BL_ARGS); break;
-            case 4: k_blend<0, 4, false, false, false><<<grid, 64, 0, s>>>(BL_ARGS); break;
-            case 5: k_blend<0, 4, false, false, true><<<grid, 64, 0, s>>>(BL_ARGS); break;
-            case 6: k_blend<0, 4, false, true, false><<<grid, 64, 0, s>>>(BL_ARGS); break;
-            case 7: k_blend<0, 4, false, true, true><<<grid, 64, 0, s>>>(BL_ARGS); break;
-            case 8: case 10: k_blend<0, 1, false, true, false><<<grid, 256, 0, s>>>(BL_ARGS); break;
-            default: k_blend<0, 1, false, true, true><<<grid, 256, 0, s>>>(BL_ARGS); break;
+        const int sk = g_blend_skip;
+        if (g_blend_ppt == 4) {
+            if (g_blend_shape8) { if (sk == 2) k_blend<0, 4, false, true, 2><<<grid, 64, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 4, false, true, 1><<<grid, 64, 0, s>>>(BL_ARGS); else k_blend<0, 4, false, true, 0><<<grid, 64, 0, s>>>(BL_ARGS); }
+            else { if (sk) k_blend<0, 4, false, false, 1><<<grid, 64, 0, s>>>(BL_ARGS); else k_blend<0, 4, false, false, 0><<<grid, 64, 0, s>>>(BL_ARGS); }
+        } else if (g_blend_ppt == 1) {
+            if (sk == 2) k_blend<0, 1, false, true, 2><<<grid, 256, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 1, false, true, 1><<<grid, 256, 0, s>>>(BL_ARGS); else k_blend<0, 1, false, true, 0><<<grid, 256, 0, s>>>(BL_ARGS);
+        } else {
+            if (g_blend_shape8) { if (sk == 2) k_blend<0, 2, false, true, 2><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 2, false, true, 1><<<grid, 128, 0, s>>>(BL_ARGS); else k_blend<0, 2, false, true, 0><<<grid, 128, 0, s>>>(BL_ARGS); }
+            else { if (sk == 2) k_blend<0, 2, false, false, 2><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 2, false, false, 1><<<grid, 128, 0, s>>>(BL_ARGS); else k_blend<0, 2, false, false, 0><<<grid, 128, 0, s>>>(BL_ARGS); }
         }
     }
 #undef BL_ARGS
