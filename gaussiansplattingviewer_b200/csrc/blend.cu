@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                     }
                 }
             };
-            if (SKIP == 2) {
+            if (SKIP >= 2) {
                 // Warp-level filter: each lane tests four records of the batch against the warp's pixel block
                 // (conservatively: splat box vs block box, 0.01 px of slack against rounding), the ballots give the
                 // hit list, and only hits run the per-pixel body.  A 16x16 tile's splat touches on average fewer
@@ -248,8 +248,36 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
                 for (int i = 0; i < NW; ++i) {
                     const int j = i * 32 + lane;
                     const float4 a = s_rec[buf][j][0];
-                    const bool keep = (j < cnt) && (a.x + a.z >= bx0) && (a.x - a.z <= bx1) && (a.y + a.w >= by0) &&
-                                      (a.y - a.w <= by1);
+                    bool keep = (j < cnt) && (a.x + a.z >= bx0) && (a.x - a.z <= bx1) && (a.y + a.w >= by0) &&
+                                (a.y - a.w <= by1);
+                    if (SKIP == 3 && MODE != 2) {
+                        // second test: can any pixel of the block reach alpha >= 1/255, i.e. is the maximum of the
+                        // (concave) exponent p2 = A x^2 + B x y + C y^2 over the block's box of centre offsets at
+                        // least -log2(255 opacity)?  The maximum over a box that does not hold the centre lies on an
+                        // edge; each edge is a 1-D parabola with a clamped vertex.  Conservative by 0.05 in log2
+                        // units; conics that are not positive definite with a margin (flag, or det < 1e-3 of its
+                        // terms) are never culled.
+                        const float4 q = s_rec[buf][j][1];
+                        const float flag = s_rec[buf][j][2].w;
+                        const float x0 = bx0 - a.x, x1 = bx1 - a.x, y0 = by0 - a.y, y1 = by1 - a.y;
+                        const bool centre_in = (x0 <= 0.f) && (x1 >= 0.f) && (y0 <= 0.f) && (y1 >= 0.f);
+                        const float ac4 = 4.f * q.x * q.z;
+                        const bool pd = (flag == 0.f) && (q.x < 0.f) && (q.z < 0.f) && (ac4 - q.y * q.y > 1e-3f * ac4);
+                        if (keep && pd && !centre_in) {
+                            const float ry = __frcp_rn(-2.f * q.z), rx = __frcp_rn(-2.f * q.x);
+                            auto edge_x = [&](float x) {  // max over y in [y0, y1] at fixed x
+                                const float y = fminf(fmaxf(q.y * x * ry, y0), y1);
+                                return fmaf(fmaf(q.z, y, q.y * x), y, q.x * x * x);
+                            };
+                            auto edge_y = [&](float y) {  // max over x in [x0, x1] at fixed y
+                                const float x = fminf(fmaxf(q.y * y * rx, x0), x1);
+                                return fmaf(fmaf(q.x, x, q.y * y), x, q.z * y * y);
+                            };
+                            const float pmax = fmaxf(fmaxf(edge_x(x0), edge_x(x1)), fmaxf(edge_y(y0), edge_y(y1)));
+                            const float theta = __log2f(255.f * q.w);  // alpha >= 1/255  <=>  p2 >= -theta
+                            keep = !(pmax < -theta - 0.05f);          // NaN anywhere keeps the splat
+                        }
+                    }
                     hits[i] = __ballot_sync(0xffffffffu, keep);
                 }
 #pragma unroll
@@ -331,18 +359,18 @@ __global__ void k_pack_disp_u16(const float4* __restrict__ rgba, uint16_t* __res
 }
 
 // kernel-variant knobs (gsr_tune): pixels per thread, warp block shape, warp-level quad skip
-int g_blend_ppt = 2, g_blend_shape8 = 1, g_blend_skip = 2;
+int g_blend_ppt = 2, g_blend_shape8 = 1, g_blend_skip = 3;
 
 }  // namespace
 
 void set_blend_ppt(int v) { if (v == 1 || v == 2 || v == 4) g_blend_ppt = v; }
 void set_blend_shape8(int v) { g_blend_shape8 = v ? 1 : 0; }
-void set_blend_skip(int v) { g_blend_skip = (v == 2) ? 2 : (v ? 1 : 0); }
+void set_blend_skip(int v) { g_blend_skip = (v >= 0 && v <= 3) ? v : 1; }
 
 // default configuration (every mode, and the counting variant)
 constexpr int BL_PPT = 2;
 constexpr bool BL_SHAPE8 = true;
-constexpr int BL_SKIP = 2;
+constexpr int BL_SKIP = 3;
 
 template <bool COUNT>
 static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
@@ -351,11 +379,14 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
     const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
     constexpr int TH = 256 / BL_PPT;
 #define BL_ARGS fp, ranges, inst_gid, sp, out_rgba, flags, pc
+    // the counting variant visits every splat of a list (no skipping), so that "pairs visited" is the algorithmic
+    // figure of SURVEY 8(d): per pixel, the list position at which it terminates
+    constexpr int SK = COUNT ? 0 : BL_SKIP;
     if (flags & GSR_FLAG_OFFICIAL_BIT) k_blend<5, BL_PPT, COUNT, BL_SHAPE8, 0><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (render_mod == -2) k_blend<2, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (render_mod == -3) k_blend<3, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (render_mod == -4) k_blend<4, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (COUNT) k_blend<0, BL_PPT, COUNT, BL_SHAPE8, BL_SKIP><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (render_mod == -2) k_blend<2, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (render_mod == -3) k_blend<3, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (render_mod == -4) k_blend<4, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
+    else if (COUNT) k_blend<0, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
     else {
         // measurement variants of the main mode
         const int sk = g_blend_skip;
@@ -365,7 +396,7 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
         } else if (g_blend_ppt == 1) {
             if (sk == 2) k_blend<0, 1, false, true, 2><<<grid, 256, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 1, false, true, 1><<<grid, 256, 0, s>>>(BL_ARGS); else k_blend<0, 1, false, true, 0><<<grid, 256, 0, s>>>(BL_ARGS);
         } else {
-            if (g_blend_shape8) { if (sk == 2) k_blend<0, 2, false, true, 2><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 2, false, true, 1><<<grid, 128, 0, s>>>(BL_ARGS); else k_blend<0, 2, false, true, 0><<<grid, 128, 0, s>>>(BL_ARGS); }
+            if (g_blend_shape8) { if (sk == 3) k_blend<0, 2, false, true, 3><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk == 2) k_blend<0, 2, false, true, 2><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 2, false, true, 1><<<grid, 128, 0, s>>>(BL_ARGS); else k_blend<0, 2, false, true, 0><<<grid, 128, 0, s>>>(BL_ARGS); }
             else { if (sk == 2) k_blend<0, 2, false, false, 2><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 2, false, false, 1><<<grid, 128, 0, s>>>(BL_ARGS); else k_blend<0, 2, false, false, 0><<<grid, 128, 0, s>>>(BL_ARGS); }
         }
     }

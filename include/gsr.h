@@ -220,7 +220,7 @@ int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* c
 #define GSR_TUNE_SORT_PREFETCH 4 /* 1 (default) = 32-bit-key radix passes use super-tiles: two 4096-key sub-tiles per look-back */
 #define GSR_TUNE_SORT_MATCH_MIX 5 /* 1 = radix ranking sends every other item through MATCH.ANY (ADU pipe) instead of ballots; default 0 (slower) */
 #define GSR_TUNE_FRAME_FORK 6 /* 1 (default) = scratch clears and the tile scan run on an auxiliary stream beside preprocess / depth sort */
-#define GSR_TUNE_BLEND_SKIP 3   /* 0 = none, 1 = warp vote per splat, 2 (default) = warp filter per batch: quads that miss the warp's pixel block */
+#define GSR_TUNE_BLEND_SKIP 3   /* 0 = none, 1 = warp vote per splat, 2 = warp filter per batch (quad vs the warp's pixel block), 3 (default) = 2 + alpha >= 1/255 reachable in the block */
 int gsr_tune(gsr_t* h, int key, int value);
 
 #ifdef __cplusplus
