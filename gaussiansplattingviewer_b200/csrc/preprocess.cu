@@ -92,7 +92,7 @@ struct SharedParams {
 };
 
 template <int SH_DIM, bool DEBUG>
-__global__ void __launch_bounds__(256) k_preprocess(const FrameParams* __restrict__ fp, SceneBuffers scene,
+__global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __restrict__ fp, SceneBuffers scene,
                                                     SplatBuffers out, FrameCounters* __restrict__ counters,
                                                     unsigned n, int sh_dim_rt) {
     __shared__ SharedParams P;

@@ -384,3 +384,32 @@ def test_full_size_properties_3m_1080p(R):
     assert np.isfinite(img).all() and img[..., 3].max() <= 1.0 and img[..., :3].min() >= 0.0
     # idempotence: same state, same image, bit for bit
     assert np.array_equal(_bits(r.draw().cpu().numpy()), _bits(img))
+
+
+@pytest.mark.parametrize("mod", [3, -1, -3])
+def test_full_size_properties_6m_4k(R, mod):
+    """BASELINE config 4 size (6M SH3, 3840x2160, modes 3 / -1 / -3): size-independent properties, and the
+    one-sort 64-bit-key path as an independent cross-check of the two-level sort at full size."""
+    g = scenes.synthetic_gaussians(6_000_000, seed=1)
+    W, H = 3840, 2160
+    r, _ = _setup(R, g, W, H, mod=mod, debug=False)
+    img = r.read_pixels_rgba32f().copy()         # host path: grows the instance buffers if mode -1 needs it
+    s = r.stats()
+    assert not s.overflow and s.n_visible > 2_000_000 and s.n_instances > 4 * s.n_visible
+    keys = r.debug_fetch(_gsr.GSR_DBG_INST_KEYS, np.uint64)
+    vals = r.debug_fetch(_gsr.GSR_DBG_INST_VALS, np.uint32)
+    ranges = r.debug_fetch(_gsr.GSR_DBG_RANGES, np.int32, 2)
+    assert len(keys) == s.n_instances
+    assert np.all(keys[1:] >= keys[:-1])
+    same = keys[1:] == keys[:-1]
+    assert np.all(vals[1:][same] > vals[:-1][same])
+    tiles = (keys >> np.uint64(32)).astype(np.int64)
+    counts = np.bincount(tiles, minlength=s.tiles_x * s.tiles_y)
+    assert s.tiles_x * s.tiles_y == 240 * 135 and np.array_equal(ranges[:, 1] - ranges[:, 0], counts)
+    assert np.isfinite(img).all() and img[..., 3].max() <= 1.0
+    if mod != -1:
+        assert img[..., :3].min() >= 0.0 and img[..., :3].max() <= 1.0
+    del keys, vals
+    r2, _ = _setup(R, g, W, H, mod=mod, keys64=True, debug=False)
+    img2 = r2.read_pixels_rgba32f()
+    assert np.array_equal(_bits(img2), _bits(img))
