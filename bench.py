@@ -352,15 +352,26 @@ def main():
                             "frac_fp32": round(blend_flops / (sm["blend"] * 1e-3) / 1e12 / fp32_peak, 4),
                             "ex2_tops": round(contributed / (sm["blend"] * 1e-3) / 1e12, 3),
                             "frac_ex2": round(contributed / (sm["blend"] * 1e-3) / 1e12 / ex2_peak, 4)})
+    # DRAM bytes per launch from the committed ncu --set full capture of the same workload (not measured in this run)
+    traffic = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tj = json.load(f)
+        if tj.get("workload") == args.workload and not args.keys64:
+            traffic = tj.get("per_stage", {})
+    except Exception:
+        traffic = {}
+    for k in stages:
+        stages[k]["ncu_dram_bytes"] = traffic.get(k)
     dom = max(sb, key=lambda k: sm[k])
     if dom == "blend":
         roof = {"kernel": "k_blend", "bound": "fp32", "achieved": stages["blend"]["fp32_tflops"], "peak": round(fp32_peak, 2),
-                "unit": "TFLOP/s", "frac": stages["blend"]["frac_fp32"], "traffic": None,
+                "unit": "TFLOP/s", "frac": stages["blend"]["frac_fp32"], "traffic": traffic.get("blend"),
                 "peak_source": "FFMA micro-benchmark in this run (gsr_measure_peaks)",
                 "alg_flops_per_launch": blend_flops, "hbm_gbs": stages["blend"]["gbs"], "hbm_frac": stages["blend"]["frac_hbm"]}
     else:
         roof = {"kernel": dom, "bound": "hbm", "achieved": stages[dom]["gbs"], "peak": hbm_peak, "unit": "GB/s",
-                "frac": stages[dom]["frac_hbm"], "traffic": None, "peak_source": peak_src,
+                "frac": stages[dom]["frac_hbm"], "traffic": traffic.get(dom), "peak_source": peak_src,
                 "alg_bytes_per_launch": stages[dom]["alg_bytes"]}
     fps = world * K / (o["ms_a"] * 1e-3)
     e2e_fps = world * K / (o["ms_b"] * 1e-3)
