@@ -44,12 +44,12 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // kernel renderer_cuda.py:212-224 calls): pixel coordinates are integers, rows run top-down, every pixel of a
 // touched tile evaluates the splat (the record carries infinite half extents), `power > 0` is always tested, a
 // pixel stops BEFORE blending the splat that would take T * (1 - alpha) below 1e-4, and alpha is written as 1.
-template <int MODE, int PPT, bool COUNT, bool SHAPE8, int SKIP>  // SKIP: 0 none, 1 warp vote per splat, 2 warp filter per batch
-__global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
+template <int MODE, int PPT, bool COUNT, bool SHAPE8, int SKIP, int TILE = 16>  // SKIP: 0 none, 1 warp vote per splat, 2 warp filter per batch
+__global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
                                                      const uint32_t* __restrict__ inst_gid, SplatBuffers sp,
                                                      float* __restrict__ out_rgba, unsigned flags,
                                                      unsigned long long* __restrict__ pair_counts) {
-    constexpr int THREADS = 256 / PPT;
+    constexpr int THREADS = TILE * TILE / PPT;
     constexpr int PER_THREAD = (BL_BATCH + THREADS - 1) / THREADS;  // records staged per thread per batch
     // one record = three consecutive float4 (48 B): the three shared-memory reads of a splat are constant
     // offsets from one running pointer
@@ -61,12 +61,12 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
     int lx, lyb;
     if (SHAPE8) {
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-        constexpr int WARPS_Y = GSR_TILE / (4 * PPT);  // warps stacked vertically per 8-column half
+        constexpr int WARPS_Y = TILE / (4 * PPT);  // warps stacked vertically per 8-column strip
         lx = (warp / WARPS_Y) * 8 + (lane & 7);
         lyb = (warp % WARPS_Y) * 4 + (lane >> 3);
     } else {
-        lx = threadIdx.x & (GSR_TILE - 1);
-        lyb = threadIdx.x / GSR_TILE;
+        lx = threadIdx.x & (TILE - 1);
+        lyb = threadIdx.x / TILE;
     }
     // pixel-centre bounds of the warp's block, widened by 0.01 px (SKIP == 2)
     float bx0, bx1, by0, by1;
@@ -74,19 +74,19 @@ __global__ void __launch_bounds__(256 / PPT) k_blend(const FrameParams* __restri
         const int warp = threadIdx.x >> 5;
         int wx0, wy0, ww, wh;
         if (SHAPE8) {
-            constexpr int WARPS_Y = GSR_TILE / (4 * PPT);
+            constexpr int WARPS_Y = TILE / (4 * PPT);
             wx0 = (warp / WARPS_Y) * 8; wy0 = (warp % WARPS_Y) * 4 * PPT; ww = 8; wh = 4 * PPT;
         } else {
-            wx0 = 0; wy0 = warp * 2 * PPT; ww = GSR_TILE; wh = 2 * PPT;
+            wx0 = 0; wy0 = warp * (32 / TILE) * PPT; ww = TILE; wh = (32 / TILE) * PPT;
         }
         constexpr float C0 = (MODE == 5) ? 0.f : 0.5f;
-        bx0 = (float)(blockIdx.x * GSR_TILE + wx0) + C0 - 0.01f;
-        bx1 = (float)(blockIdx.x * GSR_TILE + wx0 + ww - 1) + C0 + 0.01f;
-        by0 = (float)(blockIdx.y * GSR_TILE + wy0) + C0 - 0.01f;
-        by1 = (float)(blockIdx.y * GSR_TILE + wy0 + wh - 1) + C0 + 0.01f;
+        bx0 = (float)(blockIdx.x * TILE + wx0) + C0 - 0.01f;
+        bx1 = (float)(blockIdx.x * TILE + wx0 + ww - 1) + C0 + 0.01f;
+        by0 = (float)(blockIdx.y * TILE + wy0) + C0 - 0.01f;
+        by1 = (float)(blockIdx.y * TILE + wy0 + wh - 1) + C0 + 0.01f;
     }
-    const int px = blockIdx.x * GSR_TILE + lx;
-    const int py0 = blockIdx.y * GSR_TILE + lyb * PPT;  // GL row, 0 = bottom
+    const int px = blockIdx.x * TILE + lx;
+    const int py0 = blockIdx.y * TILE + lyb * PPT;  // GL row, 0 = bottom
     constexpr float CENTRE = (MODE == 5) ? 0.f : 0.5f;
     const float pxf = (float)px + CENTRE;
     float pyf[PPT], T[PPT], cr[PPT], cg[PPT], cb[PPT];
@@ -375,10 +375,21 @@ constexpr int BL_SKIP = 3;
 template <bool COUNT>
 static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                            float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
-                           unsigned long long* pc, cudaStream_t s) {
+                           unsigned long long* pc, cudaStream_t s, int tile) {
     const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
     constexpr int TH = 256 / BL_PPT;
 #define BL_ARGS fp, ranges, inst_gid, sp, out_rgba, flags, pc
+    if (tile == 32) {
+        // 32x32 tiles (shader path only): a quarter of the tiles, less than half the instances to duplicate and
+        // sort; the per-warp batch filter keeps the blend's work per 8x8 pixel block what it was
+        constexpr int SK32 = COUNT ? 0 : BL_SKIP;
+        constexpr int TH32 = 1024 / BL_PPT;
+        if (render_mod == -2) k_blend<2, BL_PPT, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
+        else if (render_mod == -3) k_blend<3, BL_PPT, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
+        else if (render_mod == -4) k_blend<4, BL_PPT, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
+        else k_blend<0, BL_PPT, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
+        return;
+    }
     // the counting variant visits every splat of a list (no skipping), so that "pairs visited" is the algorithmic
     // figure of SURVEY 8(d): per pixel, the list position at which it terminates
     constexpr int SK = COUNT ? 0 : BL_SKIP;
@@ -404,15 +415,15 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
 }
 
 void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp, float* out_rgba,
-                  int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s) {
-    launch_blend_t<false>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, nullptr, s);
+                  int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s, int tile) {
+    launch_blend_t<false>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, nullptr, s, tile);
 }
 
 // Instrumented variant: same image, plus pair_counts[0] += pairs visited, [1] += pairs that contributed.
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                         float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
-                        unsigned long long* pair_counts, cudaStream_t s) {
-    launch_blend_t<true>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pair_counts, s);
+                        unsigned long long* pair_counts, cudaStream_t s, int tile) {
+    launch_blend_t<true>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pair_counts, s, tile);
 }
 
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s) {

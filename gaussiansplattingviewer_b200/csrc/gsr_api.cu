@@ -68,7 +68,8 @@ struct gsr_renderer {
     SortScratch ss_i = {};
     uint64_t* d_dbgkeys = nullptr;
     // image-side
-    int W = 0, H = 0, tiles_x = 0, tiles_y = 0;
+    int W = 0, H = 0, tiles_x = 0, tiles_y = 0, tile = 16;  // tiling of the last frame
+    int tile_req = 32;  // gsr_tune(GSR_TUNE_TILE): tile edge of the shader path, 16 or 32 (official-mode frames always use 16)
     int2* d_ranges = nullptr;
     int* d_tile_grid = nullptr;  // (tiles_y + 1) x grid_w corner impulses
     int grid_w = 0;
@@ -244,6 +245,13 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     rc = ensure_capacity(h, std::max(h->capacity, auto_capacity(h)), keys64);
     if (rc) return rc;
     const long long N = h->N, cap = h->capacity;
+    // tile edge of this frame: buffers are sized for 16; the official rasterizer's semantics depend on 16x16 tiles
+    const int tile = (official || h->tile_req != 32) ? 16 : 32;
+    fp.tile_shift = (tile == 32) ? 5 : 4;
+    h->tiles_x = fp.tiles_x = (h->W + tile - 1) / tile;
+    h->tiles_y = fp.tiles_y = (h->H + tile - 1) / tile;
+    h->grid_w = (h->tiles_x + 1) | 1;  // odd pitch: conflict-free column walks in k_tile_scan
+    h->tile = tile;
     const int n_tiles = h->tiles_x * h->tiles_y;
     const int tbits = tile_bits(n_tiles);
     SceneBuffers scene = {h->d_xyz, h->d_rot, h->d_scale_op, h->d_sh};
@@ -338,7 +346,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
         h->launches += 1;
     }
     if (timed) cudaEventRecord(h->ev[5], s);
-    launch_blend(h->d_fp, h->d_ranges, h->d_ivals[res], h->sp, out, fp.render_mod, fp.flags, h->tiles_x, h->tiles_y, s);
+    launch_blend(h->d_fp, h->d_ranges, h->d_ivals[res], h->sp, out, fp.render_mod, fp.flags, h->tiles_x, h->tiles_y, s, tile);
     h->launches += 1;
     if (timed) cudaEventRecord(h->ev[6], s);
     CK(cudaMemcpyAsync(h->h_counters, h->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, s));
@@ -1001,6 +1009,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_SORT_PREFETCH: set_sort_prefetch(value); return 0;
         case GSR_TUNE_SORT_MATCH_MIX: set_sort_mix(value); return 0;
         case GSR_TUNE_FRAME_FORK: g_frame_fork = value ? 1 : 0; return 0;
+        case GSR_TUNE_TILE: if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32"); h->tile_req = value; h->frame_valid = false; return 0;
         case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;
         default: return fail(GSR_EINVAL, "unknown tuning key");
     }
@@ -1015,7 +1024,7 @@ int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* c
     CK(cudaMalloc(&d, 16));
     CK(cudaMemset(d, 0, 16));
     launch_blend_count(h->d_fp, h->d_ranges, h->d_ivals[h->last_result_buf], h->sp, h->d_frame, h->fp.render_mod,
-                       h->fp.flags, h->tiles_x, h->tiles_y, d, 0);
+                       h->fp.flags, h->tiles_x, h->tiles_y, d, 0, h->tile);
     unsigned long long out[2] = {0, 0};
     CK(cudaMemcpy(out, d, 16, cudaMemcpyDeviceToHost));
     cudaFree(d);

@@ -3,7 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#define GSR_TILE 16
+#define GSR_TILE 16  // smallest tile edge (buffers are sized for it); a frame uses 16 or 32, see FrameParams.tile_shift
 #define GSR_GRID_REPLICAS 16  // copies of the corner-impulse grid (CTA b adds into copy b % 16)  // pixels per tile edge (16x16 tiles, one CTA per tile in the blend kernel)
 
 // Per-frame uniforms.  Lives in device memory (written by k_set_params) so that a captured CUDA graph
@@ -19,6 +19,7 @@ struct FrameParams {
     int W, H;
     int tiles_x, tiles_y;
     unsigned flags;
+    int tile_shift;  // log2 of the tile edge in pixels: 4 (16x16) or 5 (32x32, shader path only)
 };
 
 // Device-side counters of one frame (zeroed at frame start).
@@ -124,7 +125,7 @@ template <typename KeyT>
 void launch_tile_ranges(const KeyT* sorted_keys, int key_shift, const FrameCounters* counters, long long capacity,
                         int2* ranges, int n_tiles, cudaStream_t s);
 void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
-                  float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s);
+                  float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s, int tile = 16);
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s);
 void launch_extract_r(const float* rgba, float* r, long long n_px, cudaStream_t s);
 void launch_pack_disp_u16(const float* rgba, uint16_t* d, long long n_px, cudaStream_t s);
@@ -132,7 +133,7 @@ void launch_keys64_from_ranges(const int2* ranges, int n_tiles, const uint32_t* 
                                uint64_t* out, cudaStream_t s);
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                         float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
-                        unsigned long long* pair_counts, cudaStream_t s);
+                        unsigned long long* pair_counts, cudaStream_t s, int tile = 16);
 void set_blend_ppt(int v);
 void set_blend_shape8(int v);
 void set_blend_skip(int v);

@@ -89,6 +89,7 @@ struct SharedParams {
     float scale_modifier;
     int render_mod, W, H, tiles_x, tiles_y;
     unsigned flags;
+    int tile_shift;
 };
 
 template <int SH_DIM, bool DEBUG>
@@ -102,7 +103,7 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
         P.htanx = fp->htanx; P.htany = fp->htany; P.focal = fp->focal;
         P.campos[0] = fp->campos[0]; P.campos[1] = fp->campos[1]; P.campos[2] = fp->campos[2];
         P.scale_modifier = fp->scale_modifier; P.render_mod = fp->render_mod;
-        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.tiles_y = fp->tiles_y; P.flags = fp->flags;
+        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.tiles_y = fp->tiles_y; P.flags = fp->flags; P.tile_shift = fp->tile_shift;
         s_visible = 0;
     }
     __syncthreads();
@@ -264,7 +265,8 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
         // ---- outputs
         uint2 trect = make_uint2(0u, 0u);  // tx0 | tiles wide << 16, ty0 | tiles high << 16 (0 x 0 when not ok)
         if (ok) {
-            const int tx0 = imin / GSR_TILE, tx1 = imax / GSR_TILE, ty0 = jmin / GSR_TILE, ty1 = jmax / GSR_TILE;
+            const int ts = P.tile_shift;
+            const int tx0 = imin >> ts, tx1 = imax >> ts, ty0 = jmin >> ts, ty1 = jmax >> ts;
             trect.x = (unsigned)tx0 | ((unsigned)(tx1 - tx0 + 1) << 16);
             trect.y = (unsigned)ty0 | ((unsigned)(ty1 - ty0 + 1) << 16);
             // per-tile instance counts without one atomic per tile: the rectangle is the 2D prefix sum of four
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(256) k_preprocess_official(const FrameParams* 
         P.htanx = fp->htanx; P.htany = fp->htany; P.focal = fp->focal;
         P.campos[0] = fp->campos[0]; P.campos[1] = fp->campos[1]; P.campos[2] = fp->campos[2];
         P.scale_modifier = fp->scale_modifier; P.render_mod = fp->render_mod;
-        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.tiles_y = fp->tiles_y; P.flags = fp->flags;
+        P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.tiles_y = fp->tiles_y; P.flags = fp->flags; P.tile_shift = fp->tile_shift;
         s_visible = 0;
     }
     __syncthreads();

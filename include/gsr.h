@@ -211,7 +211,7 @@ int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy
  * pairs that contributed a fragment.  Synchronises; the frame buffer passed to the last draw is untouched. */
 int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed);
 
-/* Kernel-variant knobs for measurement runs (process-wide; results are identical for every setting).
+/* Kernel-variant knobs for measurement runs (process-wide unless noted; images are identical for every setting).
  * GSR_TUNE_BLEND_PPT: pixels per thread of the blend kernel, 1, 2 or 4.
  * GSR_TUNE_SORT_SMALL_TILES: 1 = radix passes use 2048-item tiles at 5 CTAs/SM instead of 4096 at 3. */
 #define GSR_TUNE_BLEND_PPT 0
@@ -220,6 +220,7 @@ int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* c
 #define GSR_TUNE_SORT_PREFETCH 4 /* 1 (default) = 32-bit-key radix passes use super-tiles: two 4096-key sub-tiles per look-back */
 #define GSR_TUNE_SORT_MATCH_MIX 5 /* 1 = radix ranking sends every other item through MATCH.ANY (ADU pipe) instead of ballots; default 0 (slower) */
 #define GSR_TUNE_FRAME_FORK 6 /* 1 (default) = scratch clears and the tile scan run on an auxiliary stream beside preprocess / depth sort */
+#define GSR_TUNE_TILE 7 /* per handle: tile edge of the shader path in pixels, 32 (default) or 16; images are identical, the instance list, ranges and tiles_x/tiles_y of gsr_stats follow it (GSR_FLAG_OFFICIAL frames always use 16) */
 #define GSR_TUNE_BLEND_SKIP 3   /* 0 = none, 1 = warp vote per splat, 2 = warp filter per batch (quad vs the warp's pixel block), 3 (default) = 2 + alpha >= 1/255 reachable in the block */
 int gsr_tune(gsr_t* h, int key, int value);
 
