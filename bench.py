@@ -218,7 +218,16 @@ def run_ours(args):
         out["stage_ms"] = dict(zip(["preprocess", "sort_depth", "ranges", "duplicate", "sort_tiles", "blend", "total"],
                                    (acc / K).tolist()))
         out["stats"] = dict(n=n, visible=int(ss.n_visible), instances=int(ss.n_instances), tiles=ss.tiles_x * ss.tiles_y)
+        # (pixel, splat) pairs of SURVEY 8(d): per pixel, its position in the 16x16-TILE list when it terminates.
+        # The frames above use 32x32 tiles (longer lists per pixel), so the algorithmic figure is counted on a
+        # 16x16 re-render of the same pose; it does not depend on how the product cuts the list up.
+        from gaussiansplattingviewer_b200 import _gsr
+        out["pairs_own_tiling"] = r.count_pairs()
+        r.tune(_gsr.GSR_TUNE_TILE, 16)
+        r.draw()
+        torch.cuda.synchronize()
         out["pairs"] = r.count_pairs()
+        r.tune(_gsr.GSR_TUNE_TILE, 32)
         out["peaks"] = r.measure_peaks()
     out.update(rank=rank, world=world, W=W, H=H, n=n, mod=mod, K=K, Wm=Wm, renderer=r, scene=g if rank == 0 else None,
                cam=cam, pose=pose_of(Wm + K - 1))
@@ -348,6 +357,7 @@ def main():
                      "frac_hbm": round(b / (ms * 1e-3) / 1e9 / hbm_peak, 4) if ms > 0 else None}
     blend_flops = 22.0 * visited
     stages["blend"].update({"pairs_visited": int(visited), "pairs_contributed": int(contributed),
+                            "pairs_visited_32x32_lists": int(o["pairs_own_tiling"][0]),
                             "fp32_tflops": round(blend_flops / (sm["blend"] * 1e-3) / 1e12, 2),
                             "frac_fp32": round(blend_flops / (sm["blend"] * 1e-3) / 1e12 / fp32_peak, 4),
                             "ex2_tops": round(contributed / (sm["blend"] * 1e-3) / 1e12, 3),
@@ -383,7 +393,7 @@ def main():
                        "order_recomputed_every_frame": True, "poses": "orbit r=10 about the origin, one new pose per step",
                        "l2": "scene buffers (%.0f MB) exceed the 126 MB L2" % (n * 236 / 1e6),
                        "visible": st["visible"], "instances": st["instances"],
-                       "mean_tile_list": round(st["instances"] / st["tiles"], 1)},
+                       "mean_tile_list": round(st["instances"] / st["tiles"], 1), "tile_edge_px": 32},
             "clocks": o["clocks"],
             "e2e": {"value": round(e2e_fps, 2), "unit": "frames/s", "h2d_bytes_per_step": 16 * 4 * 2 + 9 * 4 + 6 * 4,
                     "d2h_bytes_per_step": W * H * 3,
