@@ -212,7 +212,7 @@ int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy
 int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed);
 
 /* Kernel-variant knobs for measurement runs (process-wide unless noted; images are identical for every setting).
- * GSR_TUNE_BLEND_PPT: pixels per thread of the blend kernel, 1, 2 or 4.
+ * GSR_TUNE_BLEND_PPT: pixels per thread of the blend kernel, 1, 2 or 4; 0 (default) = 2 on 16x16 tiles, 4 on 32x32.
  * GSR_TUNE_SORT_SMALL_TILES: 1 = radix passes use 2048-item tiles at 5 CTAs/SM instead of 4096 at 3. */
 #define GSR_TUNE_BLEND_PPT 0
 #define GSR_TUNE_SORT_SMALL_TILES 1
