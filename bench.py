@@ -281,6 +281,9 @@ def run_reference(args):
     n, W, H, mod = wl["n"], wl["w"], wl["h"], wl["mod"]
     K, Wm = args.steps, args.warmup
     use_ref = O.ref_lib() is not None
+    # rank 0 is the only rank that works here: take every core this process may run on (torchrun exports
+    # OMP_NUM_THREADS=1 for its workers)
+    O.set_num_threads(len(os.sched_getaffinity(0)))
     g_full = scenes.synthetic_gaussians(n, seed=0)
     cam = Camera(H, W)
     # bounded sample: every stride-th Gaussian at full resolution, sized from a probe so that

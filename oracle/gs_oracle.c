@@ -530,6 +530,15 @@ int gso_num_threads(void) {
 #endif
 }
 
+/* torchrun exports OMP_NUM_THREADS=1; the reference arm of bench.py runs on rank 0 alone and asks for all cores */
+void gso_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* ---- official-rasterizer semantics (GSR_FLAG_OFFICIAL) -------------------------------------------------
  * PARITY UNPINNED.  The viewer's CUDA backend (/root/reference/renderer_cuda.py:205-228) calls
  * diff_gaussian_rasterization, which is not in the reference tree, has no pinned version (README.md:29) and

@@ -179,6 +179,11 @@ def num_threads() -> int:
     return int(oracle_lib().gso_num_threads())
 
 
+def set_num_threads(n: int) -> None:
+    """OpenMP threads of the calling thread's next parallel regions (both oracle libraries share one libgomp)."""
+    oracle_lib().gso_set_num_threads(int(n))
+
+
 # ---- reference shaders compiled as C++ ---------------------------------------------------------------
 def ref_vertex(gau, cam: Camera):
     L = ref_lib()
