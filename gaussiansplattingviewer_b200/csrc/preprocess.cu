@@ -93,9 +93,16 @@ struct SharedParams {
 };
 
 template <int SH_DIM, bool DEBUG>
-__global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __restrict__ fp, SceneBuffers scene,
+__global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __restrict__ fp, SceneBuffers scene,
                                                     SplatBuffers out, FrameCounters* __restrict__ counters,
                                                     unsigned n, int sh_dim_rt) {
+    // Persistent CTAs, one chunk of 256 Gaussians per iteration (a warp owns 32 consecutive rows), every load a
+    // coalesced cp.async issued well before its use, so that the fetches run under the covariance maths:
+    //   s_sh  (per warp 32 rows x 13 float4, SH_DIM == 48)  the SH rows of the warp's visible Gaussians; a lane reads
+    //         its own row with LDS.128 (rows padded from 192 to 208 bytes: conflict-free).  A
+    //         lane-per-row LDG.128 at a 192-byte stride costs 32 L1 wavefronts per instruction and 48 registers
+    //   s_in  (per warp 24 + 32 + 32 float4)  xyz / rot / scale+opacity rows of the warp's NEXT chunk
+    extern __shared__ float4 s_dyn[];
     __shared__ SharedParams P;
     __shared__ unsigned s_visible;
     if (threadIdx.x < 16) { P.view[threadIdx.x] = fp->view[threadIdx.x]; P.proj[threadIdx.x] = fp->proj[threadIdx.x]; }
@@ -107,22 +114,89 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
         s_visible = 0;
     }
     __syncthreads();
-    const unsigned g = blockIdx.x * blockDim.x + threadIdx.x;
-    bool ok = false;
-    if (g < n) {
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    float4* const s_row = s_dyn + warp * (32 * 13 + 88);  // SH rows of this warp
+    float4* const s_in = s_row + 32 * 13;                   // xyz (24 float4), rot (32), scale+opacity (32)
+    const unsigned n_chunks = (n + 255u) >> 8;
+    // rows [first, first + 32) of the warp -> s_in (lanes past the end copy nothing; a partial xyz chunk is zero-filled)
+    auto prefetch = [&](unsigned chunk) {
+        if (chunk >= n_chunks) return;
+        const unsigned first = chunk * 256u + warp * 32u;
+        if (lane < 24u) {
+            const long long left = (long long)n * 12 - ((long long)first * 12 + lane * 16);
+            if (left > 0) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(s_in + lane);
+                const int bytes = left < 16 ? (int)left : 16;
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst),
+                             "l"(reinterpret_cast<const char*>(scene.xyz) + (size_t)first * 12 + lane * 16), "r"(bytes) : "memory");
+            }
+        }
+        if (first + lane < n) {
+            const unsigned d0 = (unsigned)__cvta_generic_to_shared(s_in + 24 + lane);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0), "l"(scene.rot + first + lane) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + 32 * 16), "l"(scene.scale_op + first + lane) : "memory");
+        }
+    };
+    prefetch(blockIdx.x);
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncwarp();
+    unsigned n_ok = 0;
+    for (unsigned chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const unsigned g = chunk * 256u + threadIdx.x;
+        const bool in = g < n;
+        const unsigned gl = in ? g : n - 1;
+        bool ok = false;
         const int sh_dim = (SH_DIM > 0) ? SH_DIM : sh_dim_rt;
         const int mod = P.render_mod;
+        int ncoef = 1;
+        if (sh_dim > 3 && mod >= 1) ncoef = 4;
+        if (sh_dim > 12 && mod >= 2) ncoef = 9;
+        if (sh_dim > 27 && mod >= 3) ncoef = 16;
+        // ---- this chunk's rows out of shared memory, then the next chunk's rows on their way into it
+        const float* const s_xyz = reinterpret_cast<const float*>(s_in);
+        const float px = s_xyz[3 * lane + 0], py = s_xyz[3 * lane + 1], pz = s_xyz[3 * lane + 2];
+        const float4 q = s_in[24 + lane];
+        const float4 so = s_in[56 + lane];
+        __syncwarp();
+        prefetch(chunk + gridDim.x);
         // ---- gau_vert.glsl:134-146: project + early cull
-        const float px = __ldg(scene.xyz + 3 * (size_t)g + 0);
-        const float py = __ldg(scene.xyz + 3 * (size_t)g + 1);
-        const float pz = __ldg(scene.xyz + 3 * (size_t)g + 2);
         const float g_pos[4] = {px, py, pz, 1.f};
         float pv[4], pc[4];
         mat4_mul_vec4(P.view, g_pos, pv);
         mat4_mul_vec4(P.proj, pv, pc);
         const float ndc0 = pc[0] / pc[3], ndc1 = pc[1] / pc[3], ndc2 = pc[2] / pc[3];
         const float lim = (float)1.3;
-        const bool culled = (fabsf(ndc0) > lim || fabsf(ndc1) > lim || fabsf(ndc2) > lim);
+        const bool culled = !in || (fabsf(ndc0) > lim || fabsf(ndc1) > lim || fabsf(ndc2) > lim);
+
+        // ---- SH staging, round 1: rows whose centre is on screen (visible for certain unless a value is not
+        // finite) are requested now, so that the fetch runs under the covariance maths; the border rows
+        // (1 < |ndc| <= 1.3) wait until `ok` is known (round 2) - most of them end up invisible
+        // 4 lanes per row, 8 rows per step: lane l copies float4 (l & 3) + 4k (k = 0..2) of row 8t + (l >> 2), so
+        // every address is one base plus an immediate and every 32-byte sector that is fetched is used in full
+        const float4* const lane_src = reinterpret_cast<const float4*>(scene.sh) +
+                                       ((size_t)(g - lane) + (lane >> 2)) * 12 + (lane & 3u);
+        const unsigned lane_dst = (unsigned)__cvta_generic_to_shared(s_row + (lane >> 2) * 13 + (lane & 3u));
+        const int nv = (ncoef * 3 + 3) >> 2;  // float4s needed: 1, 3, 7, 12
+        auto stage = [&](unsigned mask) {
+            const unsigned mrow = mask >> (lane >> 2);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                if ((mrow >> (8 * t)) & 1u) {
+#pragma unroll
+                    for (int k = 0; k < 3; ++k)
+                        if ((int)(lane & 3u) + 4 * k < nv)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(lane_dst + (t * 8 * 13 + 4 * k) * 16),
+                                         "l"(lane_src + t * 8 * 12 + 4 * k) : "memory");
+                }
+            }
+        };
+        const bool use_stage = (SH_DIM == 48) && (mod != -1);
+        bool staged = false;
+        if (use_stage) {
+            staged = !culled && (DEBUG || (fabsf(ndc0) <= 1.f && fabsf(ndc1) <= 1.f && ndc2 >= -1.f && ndc2 <= 1.f));
+            const unsigned m1 = __ballot_sync(0xffffffffu, staged);
+            if (m1) stage(m1);
+        }
 
         float vs[16];
 #pragma unroll
@@ -132,8 +206,6 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
         float conic0 = 0.f, conic1 = 0.f, conic2 = 0.f, alpha = 0.f, c0 = 0.f, c1 = 0.f, c2 = 0.f;
 
         if (!culled) {
-            const float4 q = __ldg(scene.rot + g);
-            const float4 so = __ldg(scene.scale_op + g);
             depth = -pv[2];
             const float ndcx = ndc0 + 0.f, ndcy = ndc1 + 0.f;
             // ---- :151-156 scale, computeCov3D :73-93
@@ -192,64 +264,6 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
                 const float xr = ((pcr[0] / pcr[3]) + 1.f) / 2.f;
                 const float d = fabsf(xl - xr);
                 c0 = d; c1 = d; c2 = d;
-            } else {  // :214-250 SH
-                float dx = px - P.campos[0], dy = py - P.campos[1], dz = pz - P.campos[2];
-                const float len = sqrtf((dx * dx + dy * dy) + dz * dz);
-                dx = dx / len; dy = dy / len; dz = dz / len;
-                const float* __restrict__ shp = scene.sh + (size_t)sh_dim * (size_t)g;
-                int ncoef = 1;
-                if (sh_dim > 3 && mod >= 1) ncoef = 4;
-                if (sh_dim > 12 && mod >= 2) ncoef = 9;
-                if (sh_dim > 27 && mod >= 3) ncoef = 16;
-                float sh[48];
-                if (SH_DIM == 48) {
-                    const float4* __restrict__ sh4 = reinterpret_cast<const float4*>(shp);
-                    const int nv = (ncoef * 3 + 3) >> 2;  // float4s needed: 1, 3, 7, 12
-#pragma unroll
-                    for (int k = 0; k < 12; ++k) {
-                        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (k < nv) v = __ldg(sh4 + k);
-                        sh[4 * k + 0] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
-                    }
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 48; ++k) sh[k] = (k < ncoef * 3 && k < sh_dim) ? __ldg(shp + k) : 0.f;
-                }
-#define SHV(k, ch) sh[(k) * 3 + (ch)]
-                float c[3];
-#pragma unroll
-                for (int ch = 0; ch < 3; ++ch) c[ch] = SH_C0 * SHV(0, ch);
-                if (ncoef >= 4) {
-                    const float X = dx, Y = dy, Z = dz;
-#pragma unroll
-                    for (int ch = 0; ch < 3; ++ch)
-                        c[ch] = c[ch] - SH_C1 * Y * SHV(1, ch) + SH_C1 * Z * SHV(2, ch) - SH_C1 * X * SHV(3, ch);
-                    if (ncoef >= 9) {
-                        const float xx = X * X, yy = Y * Y, zz = Z * Z;
-                        const float xy = X * Y, yz = Y * Z, xz = X * Z;
-#pragma unroll
-                        for (int ch = 0; ch < 3; ++ch)
-                            c[ch] = c[ch] + SH_C2_0 * xy * SHV(4, ch) + SH_C2_1 * yz * SHV(5, ch) +
-                                    SH_C2_2 * (2.0f * zz - xx - yy) * SHV(6, ch) + SH_C2_3 * xz * SHV(7, ch) +
-                                    SH_C2_4 * (xx - yy) * SHV(8, ch);
-                        if (ncoef >= 16) {
-#pragma unroll
-                            for (int ch = 0; ch < 3; ++ch)
-                                c[ch] = c[ch] + SH_C3_0 * Y * (3.0f * xx - yy) * SHV(9, ch) + SH_C3_1 * xy * Z * SHV(10, ch) +
-                                        SH_C3_2 * Y * (4.0f * zz - xx - yy) * SHV(11, ch) +
-                                        SH_C3_3 * Z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SHV(12, ch) +
-                                        SH_C3_4 * X * (4.0f * zz - xx - yy) * SHV(13, ch) +
-                                        SH_C3_5 * Z * (xx - yy) * SHV(14, ch) + SH_C3_6 * X * (xx - 3.0f * yy) * SHV(15, ch);
-                        }
-                    }
-                }
-#undef SHV
-                c0 = c[0] + 0.5f; c1 = c[1] + 0.5f; c2 = c[2] + 0.5f;
-            }
-            if (DEBUG) {
-                vs[0] = 1.f; vs[1] = ndcx; vs[2] = ndcy; vs[3] = ndc2; vs[4] = hx; vs[5] = hy;
-                vs[6] = conic0; vs[7] = conic1; vs[8] = conic2; vs[9] = c0; vs[10] = c1; vs[11] = c2;
-                vs[12] = alpha; vs[13] = depth;
             }
             // ---- raster set-up (oracle/gs_oracle.c setup_one): depth clip, viewport, pixel rect
             if (ndc2 >= -1.f && ndc2 <= 1.f) {
@@ -261,6 +275,68 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
                     ok = (imin <= imax && jmin <= jmax);
                 }
             }
+        }
+        // ---- SH staging, round 2 (border rows that turned out visible), then the colour of the visible rows only
+        if (use_stage) {
+            const bool late = ok && !staged;
+            const unsigned m2 = __ballot_sync(0xffffffffu, late);
+            if (m2) stage(m2);
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            __syncwarp();
+        }
+        if (!culled && mod != -1 && (ok || DEBUG)) {  // :214-250 SH
+            float dx = px - P.campos[0], dy = py - P.campos[1], dz = pz - P.campos[2];
+            const float len = sqrtf((dx * dx + dy * dy) + dz * dz);
+            dx = dx / len; dy = dy / len; dz = dz / len;
+            const float* __restrict__ shp = scene.sh + (size_t)sh_dim * (size_t)gl;
+            float sh[48];
+            if (SH_DIM == 48) {
+                const float4* my = s_row + lane * 13;
+#pragma unroll
+                for (int k = 0; k < 12; ++k) {
+                    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (k < nv) v = my[k];
+                    sh[4 * k + 0] = v.x; sh[4 * k + 1] = v.y; sh[4 * k + 2] = v.z; sh[4 * k + 3] = v.w;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 48; ++k) sh[k] = (k < ncoef * 3 && k < sh_dim) ? __ldg(shp + k) : 0.f;
+            }
+#define SHV(k, ch) sh[(k) * 3 + (ch)]
+            float c[3];
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) c[ch] = SH_C0 * SHV(0, ch);
+            if (ncoef >= 4) {
+                const float X = dx, Y = dy, Z = dz;
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch)
+                    c[ch] = c[ch] - SH_C1 * Y * SHV(1, ch) + SH_C1 * Z * SHV(2, ch) - SH_C1 * X * SHV(3, ch);
+                if (ncoef >= 9) {
+                    const float xx = X * X, yy = Y * Y, zz = Z * Z;
+                    const float xy = X * Y, yz = Y * Z, xz = X * Z;
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch)
+                        c[ch] = c[ch] + SH_C2_0 * xy * SHV(4, ch) + SH_C2_1 * yz * SHV(5, ch) +
+                                SH_C2_2 * (2.0f * zz - xx - yy) * SHV(6, ch) + SH_C2_3 * xz * SHV(7, ch) +
+                                SH_C2_4 * (xx - yy) * SHV(8, ch);
+                    if (ncoef >= 16) {
+#pragma unroll
+                        for (int ch = 0; ch < 3; ++ch)
+                            c[ch] = c[ch] + SH_C3_0 * Y * (3.0f * xx - yy) * SHV(9, ch) + SH_C3_1 * xy * Z * SHV(10, ch) +
+                                    SH_C3_2 * Y * (4.0f * zz - xx - yy) * SHV(11, ch) +
+                                    SH_C3_3 * Z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SHV(12, ch) +
+                                    SH_C3_4 * X * (4.0f * zz - xx - yy) * SHV(13, ch) +
+                                    SH_C3_5 * Z * (xx - yy) * SHV(14, ch) + SH_C3_6 * X * (xx - 3.0f * yy) * SHV(15, ch);
+                    }
+                }
+            }
+#undef SHV
+            c0 = c[0] + 0.5f; c1 = c[1] + 0.5f; c2 = c[2] + 0.5f;
+        }
+        if (DEBUG && !culled) {
+            vs[0] = 1.f; vs[1] = ndc0 + 0.f; vs[2] = ndc1 + 0.f; vs[3] = ndc2; vs[4] = hx; vs[5] = hy;
+            vs[6] = conic0; vs[7] = conic1; vs[8] = conic2; vs[9] = c0; vs[10] = c1; vs[11] = c2;
+            vs[12] = alpha; vs[13] = depth;
         }
         // ---- outputs
         uint2 trect = make_uint2(0u, 0u);  // tx0 | tiles wide << 16, ty0 | tiles high << 16 (0 x 0 when not ok)
@@ -301,14 +377,16 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
                             ((conic0 * conic2 - conic1 * conic1) > 1e-5f * (conic0 * conic2));
             out.rec2[g] = make_float4(c0, c1, c2, pd ? 0.f : 1.f);
         }
-        if (P.flags & GSR_FLAG_INTERNAL_DEPTH_ALL) {
-            const float d_all = -pv[2];
-            out.depth_key[g] = (d_all > 0.f) ? __float_as_uint(d_all) : 0xFFFFFFFFu;
-        } else {
-            out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
+        if (in) {
+            if (P.flags & GSR_FLAG_INTERNAL_DEPTH_ALL) {
+                const float d_all = -pv[2];
+                out.depth_key[g] = (d_all > 0.f) ? __float_as_uint(d_all) : 0xFFFFFFFFu;
+            } else {
+                out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
+            }
+            out.trect[g] = trect;
         }
-        out.trect[g] = trect;
-        if (DEBUG) {
+        if (DEBUG && in) {
             float4* d = reinterpret_cast<float4*>(out.dbg_vsout + 16 * (size_t)g);
             d[0] = make_float4(vs[0], vs[1], vs[2], vs[3]);
             d[1] = make_float4(vs[4], vs[5], vs[6], vs[7]);
@@ -320,10 +398,14 @@ __global__ void __launch_bounds__(256, 4) k_preprocess(const FrameParams* __rest
                              __float_as_int(clip_ok ? depth : 0.f), ok ? 1 : 0);
             e[1] = make_int4(imin, imax, jmin, jmax);
         }
+        n_ok += ok ? 1u : 0u;
+        // the next chunk's rows have landed; every lane is done with this chunk's SH rows
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncwarp();
     }
     // visible count: one atomic per CTA
-    const unsigned b = __ballot_sync(0xffffffffu, ok);
-    if ((threadIdx.x & 31) == 0 && b) atomicAdd(&s_visible, __popc(b));
+    n_ok = __reduce_add_sync(0xffffffffu, n_ok);
+    if ((threadIdx.x & 31) == 0 && n_ok) atomicAdd(&s_visible, n_ok);
     __syncthreads();
     if (threadIdx.x == 0 && s_visible) atomicAdd(&counters->n_visible, s_visible);
 }
@@ -571,14 +653,28 @@ void launch_pack_scene(const float* rot, const float* scale, const float* opacit
 void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
                        long long n, int sh_dim, cudaStream_t s) {
     if (n <= 0) return;
-    const unsigned grid = (unsigned)((n + 255) / 256);
     const bool dbg = out.dbg_vsout != nullptr;
+    // persistent CTAs: 3 per SM (8 warps x (32 x 13 + 88) float4 of staging each), chunks of 256 Gaussians round-robin
+    const int smem = 8 * (32 * 13 + 88) * (int)sizeof(float4);
+    static int sm_count = 0;
+    if (!sm_count) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+        cudaFuncSetAttribute(k_preprocess<48, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(k_preprocess<48, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(k_preprocess<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(k_preprocess<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(k_preprocess<48, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    }
+    const long long chunks = (n + 255) / 256;
+    const unsigned grid = (unsigned)(chunks < 3LL * sm_count ? chunks : 3LL * sm_count);
     if (sh_dim == 48) {
-        if (dbg) k_preprocess<48, true><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
-        else k_preprocess<48, false><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        if (dbg) k_preprocess<48, true><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        else k_preprocess<48, false><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
     } else {
-        if (dbg) k_preprocess<0, true><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
-        else k_preprocess<0, false><<<grid, 256, 0, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        if (dbg) k_preprocess<0, true><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        else k_preprocess<0, false><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
     }
 }
 
