@@ -39,6 +39,33 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+// Packed binary32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): one issue slot does the IEEE operation on two
+// pixels.  The blend is issue bound, and its FMA-pipe half packs; results are those of the scalar
+// instructions bit for bit (round-to-nearest, no contraction on either side).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ float lo2(f32x2 v) { return __uint_as_float((unsigned)(v & 0xffffffffull)); }
+__device__ __forceinline__ float hi2(f32x2 v) { return __uint_as_float((unsigned)(v >> 32)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
 // MODE: 0 = gaussian falloff (render_mod >= 0 or -1), 2 = billboard (-2), 3 = flat ball (-3), 4 = gaussian ball (-4),
 // 5 = the official rasterizer's renderCUDA rule (GSR_FLAG_OFFICIAL; diff_gaussian_rasterization forward.cu, the
 // kernel renderer_cuda.py:212-224 calls): pixel coordinates are integers, rows run top-down, every pixel of a
@@ -167,9 +194,17 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                 float dy[PPT];
                 bool in[PPT];
                 bool any_in = false;
+                if constexpr (MODE == 0 && !COUNT && PPT % 2 == 0) {
+                    const f32x2 ay2 = pk2(a.y, a.y);
+#pragma unroll
+                    for (int k = 0; k < PPT; k += 2) {
+                        const f32x2 d2 = sub2(pk2(pyf[k], pyf[k + 1]), ay2);
+                        dy[k] = lo2(d2); dy[k + 1] = hi2(d2);
+                    }
+                }
 #pragma unroll
                 for (int k = 0; k < PPT; ++k) {
-                    dy[k] = pyf[k] - a.y;
+                    if constexpr (!(MODE == 0 && !COUNT && PPT % 2 == 0)) dy[k] = pyf[k] - a.y;
                     if (COUNT) n_eval += (T[k] >= 1e-4f) ? 1u : 0u;
                     in[k] = inx && (fabsf(dy[k]) <= a.w) && (T[k] >= 1e-4f);
                     any_in = any_in || in[k];
@@ -180,6 +215,55 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                 const float4 c = rec[2];  // r, g, b, flag: conic not positive definite
                 const float bdx = q.y * dx;
                 const float adx2 = q.x * dx * dx;
+                if constexpr (MODE == 0 && !COUNT && PPT % 2 == 0) {
+                    // pixel pairs through the packed FMA pipe: 9 packed + 2 ex2 + 2 min + 4 compare/select per pair
+                    // instead of 18 + 2 + 2 + 4 scalar instructions
+                    const f32x2 bdx2 = pk2(bdx, bdx), adx22 = pk2(adx2, adx2), qz2 = pk2(q.z, q.z), qw2 = pk2(q.w, q.w);
+                    const f32x2 cx2 = pk2(c.x, c.x), cy2 = pk2(c.y, c.y), cz2 = pk2(c.z, c.z);
+#pragma unroll
+                    for (int k = 0; k < PPT; k += 2) {
+                        const f32x2 dy2 = pk2(dy[k], dy[k + 1]);
+                        const f32x2 p2 = fma2(fma2(qz2, dy2, bdx2), dy2, adx22);  // log2(e) * power
+                        const f32x2 ae = mul2(qw2, pk2(ex2_approx(lo2(p2)), ex2_approx(hi2(p2))));
+                        const float al0 = fminf(0.99f, lo2(ae)), al1 = fminf(0.99f, hi2(ae));
+                        const f32x2 T2 = pk2(T[k], T[k + 1]);
+                        const f32x2 aT = mul2(pk2(al0, al1), T2);
+                        float w0, w1;
+                        if (CHECK_POWER) {
+                            w0 = (in[k] && !(al0 < 1.f / 255.f) && !(lo2(p2) > 0.f)) ? lo2(aT) : 0.f;
+                            w1 = (in[k + 1] && !(al1 < 1.f / 255.f) && !(hi2(p2) > 0.f)) ? hi2(aT) : 0.f;
+                        } else {
+                            // one compare that ANDs in the coverage predicate, one select (the compiler otherwise
+                            // selects twice): w = (in && !(alpha < 1/255)) ? alpha * T : 0
+                            asm("{\n\t"
+                                ".reg .pred p, q;\n\t"
+                                "setp.ne.u32 q, %2, 0;\n\t"
+                                "setp.geu.and.f32 p, %1, 0f3B808081, q;\n\t"
+                                "selp.f32 %0, %3, 0f00000000, p;\n\t"
+                                "}"
+                                : "=f"(w0)
+                                : "f"(al0), "r"((unsigned)in[k]), "f"(lo2(aT)));
+                            asm("{\n\t"
+                                ".reg .pred p, q;\n\t"
+                                "setp.ne.u32 q, %2, 0;\n\t"
+                                "setp.geu.and.f32 p, %1, 0f3B808081, q;\n\t"
+                                "selp.f32 %0, %3, 0f00000000, p;\n\t"
+                                "}"
+                                : "=f"(w1)
+                                : "f"(al1), "r"((unsigned)in[k + 1]), "f"(hi2(aT)));
+                        }
+                        const f32x2 w2 = pk2(w0, w1);
+                        const f32x2 r2 = fma2(w2, cx2, pk2(cr[k], cr[k + 1]));
+                        const f32x2 g2 = fma2(w2, cy2, pk2(cg[k], cg[k + 1]));
+                        const f32x2 b2 = fma2(w2, cz2, pk2(cb[k], cb[k + 1]));
+                        const f32x2 Tn = sub2(T2, w2);
+                        cr[k] = lo2(r2); cr[k + 1] = hi2(r2);
+                        cg[k] = lo2(g2); cg[k + 1] = hi2(g2);
+                        cb[k] = lo2(b2); cb[k + 1] = hi2(b2);
+                        T[k] = lo2(Tn); T[k + 1] = hi2(Tn);
+                    }
+                    return;
+                }
 #pragma unroll
                 for (int k = 0; k < PPT; ++k) {
                     bool valid = in[k];
