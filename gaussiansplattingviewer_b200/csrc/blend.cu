@@ -39,6 +39,17 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+__device__ __forceinline__ float4 lds128(unsigned a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ unsigned lds16(unsigned a) {
+    unsigned v;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+
 // Packed binary32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): one issue slot does the IEEE operation on two
 // pixels.  The blend is issue bound, and its FMA-pipe half packs; results are those of the scalar
 // instructions bit for bit (round-to-nearest, no contraction on either side).
@@ -81,6 +92,7 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
     // one record = three consecutive float4 (48 B): the three shared-memory reads of a splat are constant
     // offsets from one running pointer
     __shared__ __align__(16) float4 s_rec[2][BL_BATCH][3];
+    __shared__ uint16_t s_hit[(SKIP >= 2) ? THREADS / 32 : 1][BL_BATCH];  // per-warp hit lists (SKIP >= 2)
     const int W = fp->W, H = fp->H;
     const int tile = blockIdx.y * gridDim.x + blockIdx.x;
     // pixel block of a warp: SHAPE8 = 8 columns x (4 * PPT) rows (compact: better quad / termination
@@ -186,9 +198,8 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
         for (int k = 0; k < PPT; ++k) live = live || (T[k] >= 1e-4f);
         auto run_batch = [&](auto tag) {
             constexpr bool CHECK_POWER = decltype(tag)::value;
-            auto splat = [&](int j) {
-                const float4* rec = &s_rec[buf][j][0];
-                const float4 a = rec[0];  // cx, cy, hx, hy
+            auto splat = [&](unsigned rec) {  // shared-window address of the record
+                const float4 a = lds128(rec);  // cx, cy, hx, hy
                 const float dx = pxf - a.x;
                 const bool inx = fabsf(dx) <= a.z;
                 float dy[PPT];
@@ -211,8 +222,8 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                 }
                 // no live pixel of this warp lies inside the quad: skip the splat for 3 instructions
                 if (SKIP == 1 && !__any_sync(0xffffffffu, any_in)) return;
-                const float4 q = rec[1];  // A', B', C' (pre-scaled conic), opacity
-                const float4 c = rec[2];  // r, g, b, flag: conic not positive definite
+                const float4 q = lds128(rec + 16);  // A', B', C' (pre-scaled conic), opacity
+                const float4 c = lds128(rec + 32);  // r, g, b, flag: conic not positive definite
                 const float bdx = q.y * dx;
                 const float adx2 = q.x * dx * dx;
                 if constexpr (MODE == 0 && !COUNT && PPT % 2 == 0) {
@@ -364,24 +375,34 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                     }
                     hits[i] = __ballot_sync(0xffffffffu, keep);
                 }
+                // The hits go to a per-warp list of record offsets in shared memory, in list order: walking it costs
+                // one LDS + pointer add per splat instead of find-first-set (BREV + FLO on the XU pipe, which the
+                // four ex2 of the body already load to 50 %), clear-lowest-bit and an index multiply.
+                uint16_t* hl = s_hit[threadIdx.x >> 5];
+                const unsigned rec_base = (unsigned)__cvta_generic_to_shared(&s_rec[buf][0][0]);  // < 64 K: fits 16 bits
+                const unsigned hl_base = (unsigned)__cvta_generic_to_shared(hl);
+                int n_hit_w = 0;
 #pragma unroll
                 for (int i = 0; i < NW; ++i) {
-                    uint32_t m = hits[i];
-                    if (m == 0u) continue;
-                    // pixels die as the batch goes on: re-check once per 32 records
-                    bool alive = false;
+                    if ((hits[i] >> lane) & 1u) hl[n_hit_w + __popc(hits[i] & ((1u << lane) - 1u))] = (uint16_t)(rec_base + (i * 32 + lane) * 48);
+                    n_hit_w += __popc(hits[i]);
+                }
+                __syncwarp();
+                for (int h0 = 0; h0 < n_hit_w; h0 += 8) {
+                    // pixels die as the batch goes on: re-check every 8 hits
+                    if (h0) {
+                        bool alive = false;
 #pragma unroll
-                    for (int k = 0; k < PPT; ++k) alive = alive || (T[k] >= 1e-4f);
-                    if (!__any_sync(0xffffffffu, alive)) break;
-                    while (m) {
-                        const int bit = __ffs(m) - 1;
-                        m &= m - 1u;
-                        splat(i * 32 + bit);
+                        for (int k = 0; k < PPT; ++k) alive = alive || (T[k] >= 1e-4f);
+                        if (!__any_sync(0xffffffffu, alive)) break;
                     }
+                    const int h1 = min(h0 + 8, n_hit_w);
+#pragma unroll 1
+                    for (unsigned p = hl_base + 2 * h0, pe = hl_base + 2 * h1; p != pe; p += 2) splat(lds16(p));
                 }
             } else {
 #pragma unroll 2
-                for (int j = 0; j < cnt; ++j) splat(j);
+                for (int j = 0; j < cnt; ++j) splat((unsigned)__cvta_generic_to_shared(&s_rec[buf][j][0]));
             }
         };
         if (__any_sync(0xffffffffu, live)) {
