@@ -27,6 +27,7 @@ GSR_TUNE_SORT_PREFETCH = 4
 GSR_TUNE_SORT_MATCH_MIX = 5
 GSR_TUNE_FRAME_FORK = 6
 GSR_TUNE_TILE = 7
+GSR_TUNE_SORT_BALANCE = 8
 
 
 class Stats(C.Structure):

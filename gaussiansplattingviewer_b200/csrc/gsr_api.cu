@@ -1008,6 +1008,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_BLEND_SKIP: set_blend_skip(value); return 0;
         case GSR_TUNE_SORT_PREFETCH: set_sort_prefetch(value); return 0;
         case GSR_TUNE_SORT_MATCH_MIX: set_sort_mix(value); return 0;
+        case GSR_TUNE_SORT_BALANCE: set_sort_balance(value); return 0;
         case GSR_TUNE_FRAME_FORK: g_frame_fork = value ? 1 : 0; return 0;
         case GSR_TUNE_TILE: if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32"); h->tile_req = value; h->frame_valid = false; return 0;
         case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;

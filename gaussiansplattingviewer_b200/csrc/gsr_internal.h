@@ -140,6 +140,7 @@ void set_blend_skip(int v);
 void set_sort_small_tiles(int v);
 void set_sort_prefetch(int v);
 void set_sort_mix(int v);
+void set_sort_balance(int v);
 int measure_peaks_impl(float* fp32_tflops, float* ex2_tops, float* copy_gbs);
 
 // ---- PLY decode (ply_decode.cu) ----------------------------------------------------------------

@@ -34,6 +34,7 @@ template <> struct RsCfg<uint32_t> { static constexpr int LARGE = 16, SMALL = 8;
 template <> struct RsCfg<uint64_t> { static constexpr int LARGE = 12, SMALL = 6; };
 int g_rs_small = 0;
 int g_rs_prefetch = 1;
+int g_rs_balance = 1;  // k_rs_pass2: 1 = equal spans per CTA (gsr_tune GSR_TUNE_SORT_BALANCE)
 int g_rs_mix = 0;  // k_rs_pass2: 1 = odd items are matched by MATCH.ANY (ADU pipe) instead of ballots (measured slower)
 
 struct RsPasses {
@@ -336,7 +337,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_pass2(const uint32_t* __re
                                                           const uint32_t* __restrict__ n_dev, long long capacity,
                                                           int shift, int bits, const uint32_t* __restrict__ hist,
                                                           uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_cur,
-                                                          uint32_t* __restrict__ status_next, int mix) {
+                                                          uint32_t* __restrict__ status_next, int mix, int balance) {
     constexpr int TILE = RS_THREADS * ITEMS;  // one sub-tile
     extern __shared__ __align__(16) unsigned char s_dyn[];
     uint32_t* s_keys = reinterpret_cast<uint32_t*>(s_dyn);  // [S][TILE] tile-sorted keys
@@ -356,19 +357,33 @@ __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_pass2(const uint32_t* __re
 
     s_global_excl[t] = block_excl_scan_256(hist[t], s_tmp, nullptr);
 
+    // Balanced spans: a super-tile covers `span` <= S * TILE items, chosen so that every CTA of the grid gets the
+    // same number of equally long super-tiles.  With the full 8192-item span 3 M keys are 367 super-tiles on 444
+    // CTA slots - SMs holding three of them rank 1.5x longer than SMs holding two, and in a single-wave pass
+    // everybody's look-back waits for the slowest count row.
+    long long span = (long long)S * TILE;
+    if (balance) {
+        const long long G = gridDim.x;
+        const long long waves = (n + G * span - 1) / (G * span);
+        long long sp = (n + G * waves - 1) / (G * (waves > 0 ? waves : 1));
+        sp = (sp + 31) & ~31ll;  // 128-byte aligned warp loads
+        span = sp < TILE ? TILE : (sp > span ? span : sp);  // >= TILE: the cleared look-back rows are n / TILE
+    }
+
     while (true) {
         if (t == 0) s_tile = atomicAdd(ticket, 1u);
         __syncthreads();
         const long long tile = s_tile;  // super-tile index
-        const long long super_base = tile * (long long)(S * TILE);
+        const long long super_base = tile * span;
         if (super_base >= n) break;
+        const long long super_end = (super_base + span < n) ? super_base + span : n;
         status_next[tile * 256 + t] = 0;
         uint32_t cnt[S], dst[S];  // digit t of sub-tile s: valid count, start inside the sorted sub-tile
         int n_valid[S];
 #pragma unroll
         for (int sub = 0; sub < S; ++sub) {
             const long long tile_base = super_base + (long long)sub * TILE;
-            n_valid[sub] = (int)((n - tile_base < TILE) ? ((n - tile_base > 0) ? (n - tile_base) : 0) : TILE);
+            n_valid[sub] = (int)((super_end - tile_base < TILE) ? ((super_end - tile_base > 0) ? (super_end - tile_base) : 0) : TILE);
             cnt[sub] = 0; dst[sub] = 0;
             if (n_valid[sub] == 0) continue;  // block-uniform
 #pragma unroll
@@ -380,7 +395,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_pass2(const uint32_t* __re
 #pragma unroll
             for (int i = 0; i < ITEMS; ++i) {
                 const long long idx = warp_base + i * 32 + lane;
-                const bool valid = idx < n;
+                const bool valid = idx < super_end;
                 key[i] = valid ? keys_in[idx] : 0xFFFFFFFFu;
                 if (IDENTITY_VALS) val[i] = (uint32_t)idx;
                 else val[i] = valid ? vals_in[idx] : 0u;
@@ -489,6 +504,7 @@ int num_sms() {
 void set_sort_small_tiles(int v) { g_rs_small = v ? 1 : 0; }
 void set_sort_prefetch(int v) { g_rs_prefetch = v ? 1 : 0; }
 void set_sort_mix(int v) { g_rs_mix = v ? 1 : 0; }
+void set_sort_balance(int v) { g_rs_balance = v ? 1 : 0; }
 
 size_t sort_scratch_bytes(long long max_items, int key_bytes) {
     const int items = (key_bytes == 8) ? RsCfg<uint64_t>::SMALL : RsCfg<uint32_t>::SMALL;
@@ -598,7 +614,8 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
     int pf_ctas = 0;
     if (sizeof(KeyT) == 4 && !small && g_rs_prefetch) pf_ctas = rs2_ctas_per_sm();
     const int per_sm = pf_ctas > 0 ? pf_ctas : (small ? 5 : 3);  // resident CTAs per SM: persistent CTAs, one wave
-    const long long work_tiles = pf_ctas > 0 ? (tiles_upper + RS2_S - 1) / RS2_S : tiles_upper;
+    // balanced spans are never shorter than one sub-tile, so up to tiles_upper CTAs can have work
+    const long long work_tiles = pf_ctas > 0 ? (g_rs_balance ? tiles_upper : (tiles_upper + RS2_S - 1) / RS2_S) : tiles_upper;
     long long grid = work_tiles < (long long)sms * per_sm ? work_tiles : (long long)sms * per_sm;
     if (grid < 1) grid = 1;
     const KeyT* kin = keys_first; KeyT* kout = keys_tmp; KeyT* kother = keys;
@@ -613,11 +630,11 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
                 if (identity)
                     k_rs_pass2<RS2_ITEMS, RS2_S, true><<<(unsigned)grid, RS_THREADS, RS2_SMEM, stream>>>(
                         kin, kout, nullptr, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
-                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next, g_rs_mix);
+                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
                 else
                     k_rs_pass2<RS2_ITEMS, RS2_S, false><<<(unsigned)grid, RS_THREADS, RS2_SMEM, stream>>>(
                         kin, kout, vin, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
-                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next, g_rs_mix);
+                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
             }
         } else if (small)
             launch_pass<KeyT, RsCfg<KeyT>::SMALL>(identity, (unsigned)grid, stream, kin, kout, vin, vout, n_host, n_dev, capacity,

@@ -27,5 +27,7 @@ def run(tag):
 
 run("default")
 T = _gsr
-for pf in (0, 1, 0, 1):
-    r.tune(T.GSR_TUNE_SORT_PREFETCH, pf); run(f"sort_prefetch={pf}")
+knob = sys.argv[4] if len(sys.argv) > 4 else "GSR_TUNE_SORT_PREFETCH"
+vals = [int(v) for v in sys.argv[5].split(",")] if len(sys.argv) > 5 else [0, 1, 0, 1]
+for v in vals:
+    r.tune(getattr(T, knob), v); run(f"{knob[9:].lower()}={v}")
