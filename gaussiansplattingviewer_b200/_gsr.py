@@ -28,6 +28,7 @@ GSR_TUNE_SORT_MATCH_MIX = 5
 GSR_TUNE_FRAME_FORK = 6
 GSR_TUNE_TILE = 7
 GSR_TUNE_SORT_BALANCE = 8
+GSR_TUNE_FUSED_DEPTH_HIST = 9
 
 
 class Stats(C.Structure):

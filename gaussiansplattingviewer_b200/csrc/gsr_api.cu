@@ -109,6 +109,7 @@ struct gsr_renderer {
 
 namespace {
 
+int g_fused_depth_hist = 1;  // gsr_tune(GSR_TUNE_FUSED_DEPTH_HIST): 0 = the depth sort runs its own histogram kernel
 int g_frame_fork = 1;  // gsr_tune(GSR_TUNE_FRAME_FORK): 0 = every frame runs on one stream
 
 int free_gaussian_buffers(gsr_t* h) {
@@ -278,6 +279,13 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     }
     launch_set_params(h->d_fp, fp, h->d_counters, s);
     CK(cudaMemsetAsync(h->d_tile_grid, 0, sizeof(int) * (size_t)sp.grid_stride * GSR_GRID_REPLICAS, s));
+    // the shader-path preprocess kernel also counts the digits of the depth keys it writes (k_rs_hist is not run)
+    const bool fused_hist = g_fused_depth_hist && !keys64 && !official && order_mode != 2;
+    sp.depth_hist = nullptr;
+    if (fused_hist) {
+        sp.depth_hist = h->ss_n.hist;
+        CK(cudaMemsetAsync(h->ss_n.hist, 0, 4 * 256 * sizeof(uint32_t), s));
+    }
     if (official) launch_preprocess_official(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     else launch_preprocess(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     h->launches += 2;
@@ -290,10 +298,10 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     if (!keys64) {
         // depth sort of the N Gaussians (culled ones carry key 0xFFFFFFFF and sort to the end)
         // (the two mantissa bytes of a depth key are spread over their bins, the exponent bytes are not)
-        SortOptions so_n = {0, false, false, 0x3u, fork};
+        SortOptions so_n = {0, fused_hist, false, 0x3u, fork};
         SortOptions so = {scan_hist ? bits0 : 0, scan_hist, true, 0u, fork};
         if (fork) {
-            if (order_mode != 2) sort_scratch_clear<uint32_t>(&h->ss_n, N, false, sa);
+            if (order_mode != 2) sort_scratch_clear<uint32_t>(&h->ss_n, N, fused_hist, sa);
             sort_scratch_clear<uint32_t>(&h->ss_i, sort_upper, scan_hist, sa);
             CK(cudaEventRecord(h->ev_cleared, sa));
             CK(cudaEventRecord(h->ev_pre, s));
@@ -1009,6 +1017,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_SORT_PREFETCH: set_sort_prefetch(value); return 0;
         case GSR_TUNE_SORT_MATCH_MIX: set_sort_mix(value); return 0;
         case GSR_TUNE_SORT_BALANCE: set_sort_balance(value); return 0;
+        case GSR_TUNE_FUSED_DEPTH_HIST: g_fused_depth_hist = value ? 1 : 0; return 0;
         case GSR_TUNE_FRAME_FORK: g_frame_fork = value ? 1 : 0; return 0;
         case GSR_TUNE_TILE: if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32"); h->tile_req = value; h->frame_valid = false; return 0;
         case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;

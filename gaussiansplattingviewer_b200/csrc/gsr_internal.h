@@ -61,6 +61,7 @@ struct SplatBuffers {
     int grid_stride;      // ints per replica; GSR_GRID_REPLICAS replicas spread the atomics of hot tiles
     float* dbg_vsout;     // N x 16 or nullptr
     int32_t* dbg_setup;   // N x 8 or nullptr
+    uint32_t* depth_hist; // [4][256] digit counts of the depth keys, accumulated by k_preprocess (nullptr: not wanted)
 };
 
 // ---- radix sort (radix_sort.cu) ----------------------------------------------------------------

@@ -105,6 +105,12 @@ __global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __rest
     extern __shared__ float4 s_dyn[];
     __shared__ SharedParams P;
     __shared__ unsigned s_visible;
+    // digit counts of the depth keys this CTA writes (the four passes of the depth sort need them): the CTAs are
+    // persistent, so the counts stay in shared memory for the whole kernel and go out once per CTA - the depth
+    // sort's histogram kernel (32 us over 3 M keys, bound by shared-memory atomics) is not launched
+    __shared__ uint32_t s_dh[4 * 256];
+    for (int i = threadIdx.x; i < 4 * 256; i += 256) s_dh[i] = 0;
+    unsigned n_culled = 0;
     if (threadIdx.x < 16) { P.view[threadIdx.x] = fp->view[threadIdx.x]; P.proj[threadIdx.x] = fp->proj[threadIdx.x]; }
     if (threadIdx.x == 32) {
         P.htanx = fp->htanx; P.htany = fp->htany; P.focal = fp->focal;
@@ -378,13 +384,25 @@ __global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __rest
             out.rec2[g] = make_float4(c0, c1, c2, pd ? 0.f : 1.f);
         }
         if (in) {
+            uint32_t dk;
             if (P.flags & GSR_FLAG_INTERNAL_DEPTH_ALL) {
                 const float d_all = -pv[2];
-                out.depth_key[g] = (d_all > 0.f) ? __float_as_uint(d_all) : 0xFFFFFFFFu;
+                dk = (d_all > 0.f) ? __float_as_uint(d_all) : 0xFFFFFFFFu;
             } else {
-                out.depth_key[g] = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
+                dk = ok ? __float_as_uint(depth) : 0xFFFFFFFFu;
             }
+            out.depth_key[g] = dk;
             out.trect[g] = trect;
+            if (out.depth_hist) {
+                if (dk != 0xFFFFFFFFu) {
+                    atomicAdd(&s_dh[dk & 255u], 1u);
+                    atomicAdd(&s_dh[256 + ((dk >> 8) & 255u)], 1u);
+                    atomicAdd(&s_dh[512 + ((dk >> 16) & 255u)], 1u);
+                    atomicAdd(&s_dh[768 + (dk >> 24)], 1u);
+                } else {
+                    ++n_culled;  // key 0xFFFFFFFF: digit 255 of every pass, added once per CTA below
+                }
+            }
         }
         if (DEBUG && in) {
             float4* d = reinterpret_cast<float4*>(out.dbg_vsout + 16 * (size_t)g);
@@ -408,6 +426,18 @@ __global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __rest
     if ((threadIdx.x & 31) == 0 && n_ok) atomicAdd(&s_visible, n_ok);
     __syncthreads();
     if (threadIdx.x == 0 && s_visible) atomicAdd(&counters->n_visible, s_visible);
+    if (out.depth_hist) {
+        n_culled = __reduce_add_sync(0xffffffffu, n_culled);
+        if ((threadIdx.x & 31) == 0 && n_culled) {
+            atomicAdd(&s_dh[255], n_culled); atomicAdd(&s_dh[256 + 255], n_culled);
+            atomicAdd(&s_dh[512 + 255], n_culled); atomicAdd(&s_dh[768 + 255], n_culled);
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 4 * 256; i += 256) {
+            const uint32_t c = s_dh[i];
+            if (c) atomicAdd(&out.depth_hist[i], c);
+        }
+    }
 }
 
 // ---- official-rasterizer semantics (GSR_FLAG_OFFICIAL) ---------------------------------------------------
