@@ -430,3 +430,27 @@ def test_tile_edge_16_and_32_give_identical_images(R, mod, sm):
         s = r.stats()
         assert (s.tiles_x, s.tiles_y) == ((W + tile - 1) // tile, (H + tile - 1) // tile)
     assert np.array_equal(_bits(imgs[0]), _bits(imgs[1]))
+
+
+def test_sort_balance_and_fused_histogram_knobs_change_nothing(R):
+    """The equal-span radix passes and the depth-digit histogram kept by the preprocess kernel are
+    performance variants: instance list, ranges and image are bit-identical to the fixed-tile passes
+    with the sort's own histogram kernel (ragged N: last span partial, culled keys in every pass)."""
+    g = _awkward_scene(300_007, seed=31)
+    W, H = 1280, 720
+    out = []
+    for balance, fused in [(1, 1), (0, 0), (0, 1), (1, 0)]:
+        r, _ = _setup(R, g, W, H, debug=False)
+        r.tune(_gsr.GSR_TUNE_SORT_BALANCE, balance)
+        r.tune(_gsr.GSR_TUNE_FUSED_DEPTH_HIST, fused)
+        try:
+            img = r.draw().cpu().numpy()
+            out.append((_bits(img), r.debug_fetch(_gsr.GSR_DBG_INST_VALS, np.uint32),
+                        r.debug_fetch(_gsr.GSR_DBG_RANGES, np.int32)))
+        finally:
+            r.tune(_gsr.GSR_TUNE_SORT_BALANCE, 1)
+            r.tune(_gsr.GSR_TUNE_FUSED_DEPTH_HIST, 1)
+    for o in out[1:]:
+        for a, b in zip(out[0], o):
+            assert np.array_equal(a, b)
+    assert len(out[0][1]) > 0
