@@ -408,6 +408,29 @@ def main():
             "peaks": {"hbm_gbs": hbm_peak, "hbm_source": peak_src, "fp32_tflops": round(fp32_peak, 2),
                       "ex2_tops": round(ex2_peak, 3), "copy_gbs_this_run": round(copy_gbs, 1)},
             "scene_broadcast_ms": round(o["t_bcast_ms"], 3)}
+    # BASELINE.json's metric also names "sort Gkeys/s": the two sorts inside the frame (keys through a complete
+    # key/value sort per second: 32 depth bits over N, the tile bits over D) and, at N=1, the standalone
+    # gsr_sort_pairs on 2^24 random 32-bit keys with 32-bit values (all 32 bits, CUDA events, best of 5)
+    line["sort"] = {"depth_sort_gkeys_s": round(n / (sm["sort_depth"] * 1e-3) / 1e9, 2) if sm["sort_depth"] > 0 else None,
+                    "tile_sort_gkeys_s": round(st["instances"] / (sm["sort_tiles"] * 1e-3) / 1e9, 2) if sm["sort_tiles"] > 0 else None}
+    if world == 1:
+        import torch
+        m = 1 << 24
+        gen = torch.Generator(device="cuda").manual_seed(1)
+        best = None
+        for _ in range(5):
+            tk = torch.randint(-2 ** 31, 2 ** 31 - 1, (m,), dtype=torch.int32, device="cuda", generator=gen)
+            tv = torch.arange(m, dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            o["renderer"].sort_pairs(tk, tv)
+            e1.record()
+            torch.cuda.synchronize()
+            t = e0.elapsed_time(e1)
+            best = t if best is None else min(best, t)
+        line["sort"]["pairs_2p24_u32_gkeys_s"] = round(m / (best * 1e-3) / 1e9, 2)
+        line["sort"]["pairs_2p24_u32_ms"] = round(best, 4)
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as O
         img, t_sort, t_rast = cpu_frame(o["scene"], o["cam"], o["pose"], W, H, o["mod"], use_ref=False)
