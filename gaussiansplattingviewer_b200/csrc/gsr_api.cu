@@ -277,15 +277,12 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
         CK(cudaEventRecord(h->ev_start, s));
         CK(cudaStreamWaitEvent(sa, h->ev_start, 0));
     }
-    launch_set_params(h->d_fp, fp, h->d_counters, s);
-    CK(cudaMemsetAsync(h->d_tile_grid, 0, sizeof(int) * (size_t)sp.grid_stride * GSR_GRID_REPLICAS, s));
     // the shader-path preprocess kernel also counts the digits of the depth keys it writes (k_rs_hist is not run)
     const bool fused_hist = g_fused_depth_hist && !keys64 && !official && order_mode != 2;
-    sp.depth_hist = nullptr;
-    if (fused_hist) {
-        sp.depth_hist = h->ss_n.hist;
-        CK(cudaMemsetAsync(h->ss_n.hist, 0, 4 * 256 * sizeof(uint32_t), s));
-    }
+    sp.depth_hist = fused_hist ? h->ss_n.hist : nullptr;
+    // uniforms, counters, and the clears of the corner-impulse grid and of those histograms in one launch
+    launch_set_params(h->d_fp, fp, h->d_counters, s, h->d_tile_grid, (long long)sp.grid_stride * GSR_GRID_REPLICAS,
+                      sp.depth_hist, 4 * 256);
     if (official) launch_preprocess_official(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     else launch_preprocess(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     h->launches += 2;

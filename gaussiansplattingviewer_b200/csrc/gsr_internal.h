@@ -105,7 +105,8 @@ void launch_tile_scan(int* grid, int grid_stride, int gw, int tiles_x, int tiles
                       uint32_t* hist, FrameCounters* counters, cudaStream_t s);
 
 // ---- kernels' host launchers ---------------------------------------------------------------------
-void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s);
+void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s,
+                       int* zero_a = nullptr, long long na = 0, uint32_t* zero_b = nullptr, int nb = 0);
 void launch_pack_scene(const float* rot, const float* scale, const float* opacity, float4* rot4, float4* scale_op,
                        long long n, cudaStream_t s);
 void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,

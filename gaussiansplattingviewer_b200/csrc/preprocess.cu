@@ -632,11 +632,19 @@ __global__ void __launch_bounds__(256) k_preprocess_official(const FrameParams* 
     if (threadIdx.x == 0 && s_visible) atomicAdd(&counters->n_visible, s_visible);
 }
 
-__global__ void k_set_params(FrameParams* dst, FrameParams fp, FrameCounters* counters) {
-    if (threadIdx.x == 0) {
+// Frame start: uniforms + counters, and the two scratch clears the preprocess kernel needs before it runs (the
+// corner-impulse grid and the depth-digit histograms) - one launch instead of a kernel and two memsets in front
+// of the frame's first real kernel.
+__global__ void __launch_bounds__(256) k_set_params(FrameParams* dst, FrameParams fp, FrameCounters* counters,
+                                                    int* __restrict__ zero_a, long long na, uint32_t* __restrict__ zero_b, int nb) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         *dst = fp;
         if (counters) { counters->n_visible = 0; counters->n_instances = 0; counters->overflow = 0; counters->n_sort = 0; }
     }
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (long long i = first; i < na; i += stride) zero_a[i] = 0;
+    for (long long i = first; i < nb; i += stride) zero_b[i] = 0u;
 }
 
 __global__ void k_pack_scene(const float* __restrict__ rot, const float* __restrict__ scale,
@@ -670,8 +678,13 @@ __global__ void k_depth_keys(const float* __restrict__ xyz, View16 vm, uint32_t*
 
 }  // namespace
 
-void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s) {
-    k_set_params<<<1, 32, 0, s>>>(dst, fp, counters);
+void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s, int* zero_a,
+                       long long na, uint32_t* zero_b, int nb) {
+    const long long work = (na > nb ? na : nb);
+    long long grid = (work + 255) / 256;
+    if (grid < 1) grid = 1;
+    if (grid > 296) grid = 296;
+    k_set_params<<<(unsigned)grid, 256, 0, s>>>(dst, fp, counters, zero_a, zero_a ? na : 0, zero_b, zero_b ? nb : 0);
 }
 
 void launch_pack_scene(const float* rot, const float* scale, const float* opacity, float4* rot4, float4* scale_op,
