@@ -29,6 +29,7 @@ GSR_TUNE_FRAME_FORK = 6
 GSR_TUNE_TILE = 7
 GSR_TUNE_SORT_BALANCE = 8
 GSR_TUNE_FUSED_DEPTH_HIST = 9
+GSR_TUNE_PDL = 10
 
 
 class Stats(C.Structure):

@@ -57,6 +57,7 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
                                                           uint32_t* __restrict__ out_gid, unsigned n,
                                                           unsigned long long capacity, uint4* __restrict__ big_list,
                                                           uint32_t* __restrict__ big_count) {
+    pdl_wait();  // no global memory access before this (programmatic dependent launch)
     __shared__ uint32_t s_warp[DUP_WARPS + 1];
     __shared__ uint32_t s_chunk;
     __shared__ unsigned long long s_prefix;
@@ -222,6 +223,7 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate_big(const FrameParams
                                                               const uint32_t* __restrict__ big_count,
                                                               void* __restrict__ out_keys, uint32_t* __restrict__ out_gid,
                                                               unsigned long long capacity) {
+    pdl_wait();  // resident behind k_duplicate, which fills the list
     const uint32_t nb = *big_count;
     const uint32_t tiles_x = (uint32_t)fp->tiles_x;
     const uint32_t lane = threadIdx.x & 31;
@@ -438,12 +440,11 @@ void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, 
     if (n <= 0) return;
     const long long chunks = (n + DUP_CHUNK - 1) / DUP_CHUNK;
     long long grid = chunks < (long long)sm_count() * 6 ? chunks : (long long)sm_count() * 6;
-    k_duplicate<false><<<(unsigned)grid, DUP_THREADS, 0, s>>>(fp, sorted_gid, sp, counters,
-                                                             reinterpret_cast<unsigned long long*>(chain_status),
-                                                             chain_ticket, out_tile, out_gid, (unsigned)n,
-                                                             (unsigned long long)capacity, big_list, big_count);
-    k_duplicate_big<false><<<sm_count() * 4, DUP_THREADS, 0, s>>>(fp, sp, big_list, big_count, out_tile, out_gid,
-                                                                 (unsigned long long)capacity);
+    launch_pdl_m(2, k_duplicate<false>, dim3((unsigned)grid), dim3(DUP_THREADS), 0, s, fp, sorted_gid, sp, counters,
+               reinterpret_cast<unsigned long long*>(chain_status), chain_ticket, (void*)out_tile, out_gid, (unsigned)n,
+               (unsigned long long)capacity, big_list, (uint32_t*)big_count);
+    launch_pdl_m(2, k_duplicate_big<false>, dim3((unsigned)(sm_count() * 4)), dim3(DUP_THREADS), 0, s, fp, sp,
+               (const uint4*)big_list, (const uint32_t*)big_count, (void*)out_tile, out_gid, (unsigned long long)capacity);
 }
 
 void launch_duplicate_keys64(const FrameParams* fp, SplatBuffers sp, FrameCounters* counters, uint32_t* chain_status,

@@ -93,6 +93,7 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
     // offsets from one running pointer
     __shared__ __align__(16) float4 s_rec[2][BL_BATCH][3];
     __shared__ uint16_t s_hit[(SKIP >= 2) ? THREADS / 32 : 1][BL_BATCH];  // per-warp hit lists (SKIP >= 2)
+    pdl_wait();  // may be resident behind the last radix pass: no global memory access before this
     const int W = fp->W, H = fp->H;
     const int tile = blockIdx.y * gridDim.x + blockIdx.x;
     // pixel block of a warp: SHAPE8 = 8 columns x (4 * PPT) rows (compact: better quad / termination
@@ -491,32 +492,32 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
         // 64x64 tiles were tried too: duplicate + tile sort 0.18 -> 0.15 ms, blend 0.238 -> 0.330 ms - not kept.
         constexpr int SK32 = COUNT ? 0 : BL_SKIP;
         constexpr int P32 = 4, TH32 = 1024 / P32;
-        if (render_mod == -2) k_blend<2, P32, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
-        else if (render_mod == -3) k_blend<3, P32, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
-        else if (render_mod == -4) k_blend<4, P32, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
-        else if (!COUNT && g_blend_ppt == 2) k_blend<0, 2, false, true, BL_SKIP, 32><<<grid, 512, 0, s>>>(BL_ARGS);
-        else k_blend<0, P32, COUNT, true, SK32, 32><<<grid, TH32, 0, s>>>(BL_ARGS);
+        if (render_mod == -2) launch_pdl_m(4, k_blend<2, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
+        else if (render_mod == -3) launch_pdl_m(4, k_blend<3, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
+        else if (render_mod == -4) launch_pdl_m(4, k_blend<4, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
+        else if (!COUNT && g_blend_ppt == 2) launch_pdl_m(4, k_blend<0, 2, false, true, BL_SKIP, 32>, dim3(grid), dim3(512), 0, s, BL_ARGS);
+        else launch_pdl_m(4, k_blend<0, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
         return;
     }
     // the counting variant visits every splat of a list (no skipping), so that "pairs visited" is the algorithmic
     // figure of SURVEY 8(d): per pixel, the list position at which it terminates
     constexpr int SK = COUNT ? 0 : BL_SKIP;
-    if (flags & GSR_FLAG_OFFICIAL_BIT) k_blend<5, BL_PPT, COUNT, BL_SHAPE8, 0><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (render_mod == -2) k_blend<2, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (render_mod == -3) k_blend<3, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (render_mod == -4) k_blend<4, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
-    else if (COUNT) k_blend<0, BL_PPT, COUNT, BL_SHAPE8, SK><<<grid, TH, 0, s>>>(BL_ARGS);
+    if (flags & GSR_FLAG_OFFICIAL_BIT) launch_pdl_m(4, k_blend<5, BL_PPT, COUNT, BL_SHAPE8, 0>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
+    else if (render_mod == -2) launch_pdl_m(4, k_blend<2, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
+    else if (render_mod == -3) launch_pdl_m(4, k_blend<3, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
+    else if (render_mod == -4) launch_pdl_m(4, k_blend<4, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
+    else if (COUNT) launch_pdl_m(4, k_blend<0, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
     else {
         // measurement variants of the main mode
         const int sk = g_blend_skip;
         if (g_blend_ppt == 4) {
-            if (g_blend_shape8) { if (sk == 2) k_blend<0, 4, false, true, 2><<<grid, 64, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 4, false, true, 1><<<grid, 64, 0, s>>>(BL_ARGS); else k_blend<0, 4, false, true, 0><<<grid, 64, 0, s>>>(BL_ARGS); }
-            else { if (sk) k_blend<0, 4, false, false, 1><<<grid, 64, 0, s>>>(BL_ARGS); else k_blend<0, 4, false, false, 0><<<grid, 64, 0, s>>>(BL_ARGS); }
+            if (g_blend_shape8) { if (sk == 2) launch_pdl_m(4, k_blend<0, 4, false, true, 2>, dim3(grid), dim3(64), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 4, false, true, 1>, dim3(grid), dim3(64), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 4, false, true, 0>, dim3(grid), dim3(64), 0, s, BL_ARGS); }
+            else { if (sk) launch_pdl_m(4, k_blend<0, 4, false, false, 1>, dim3(grid), dim3(64), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 4, false, false, 0>, dim3(grid), dim3(64), 0, s, BL_ARGS); }
         } else if (g_blend_ppt == 1) {
-            if (sk == 2) k_blend<0, 1, false, true, 2><<<grid, 256, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 1, false, true, 1><<<grid, 256, 0, s>>>(BL_ARGS); else k_blend<0, 1, false, true, 0><<<grid, 256, 0, s>>>(BL_ARGS);
+            if (sk == 2) launch_pdl_m(4, k_blend<0, 1, false, true, 2>, dim3(grid), dim3(256), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 1, false, true, 1>, dim3(grid), dim3(256), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 1, false, true, 0>, dim3(grid), dim3(256), 0, s, BL_ARGS);
         } else {
-            if (g_blend_shape8) { if (sk == 3) k_blend<0, 2, false, true, 3><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk == 2) k_blend<0, 2, false, true, 2><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 2, false, true, 1><<<grid, 128, 0, s>>>(BL_ARGS); else k_blend<0, 2, false, true, 0><<<grid, 128, 0, s>>>(BL_ARGS); }
-            else { if (sk == 2) k_blend<0, 2, false, false, 2><<<grid, 128, 0, s>>>(BL_ARGS); else if (sk) k_blend<0, 2, false, false, 1><<<grid, 128, 0, s>>>(BL_ARGS); else k_blend<0, 2, false, false, 0><<<grid, 128, 0, s>>>(BL_ARGS); }
+            if (g_blend_shape8) { if (sk == 3) launch_pdl_m(4, k_blend<0, 2, false, true, 3>, dim3(grid), dim3(128), 0, s, BL_ARGS); else if (sk == 2) launch_pdl_m(4, k_blend<0, 2, false, true, 2>, dim3(grid), dim3(128), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 2, false, true, 1>, dim3(grid), dim3(128), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 2, false, true, 0>, dim3(grid), dim3(128), 0, s, BL_ARGS); }
+            else { if (sk == 2) launch_pdl_m(4, k_blend<0, 2, false, false, 2>, dim3(grid), dim3(128), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 2, false, false, 1>, dim3(grid), dim3(128), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 2, false, false, 0>, dim3(grid), dim3(128), 0, s, BL_ARGS); }
         }
     }
 #undef BL_ARGS

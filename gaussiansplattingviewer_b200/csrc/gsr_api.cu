@@ -107,6 +107,8 @@ struct gsr_renderer {
     int sortp_keybytes = 0;
 };
 
+int g_pdl = 11;  // gsr_tune(GSR_TUNE_PDL): bit 0 radix passes, 1 duplicate, 2 blend (measured slower: off), 3 preprocess; 0 = plain launches
+
 namespace {
 
 int g_fused_depth_hist = 1;  // gsr_tune(GSR_TUNE_FUSED_DEPTH_HIST): 0 = the depth sort runs its own histogram kernel
@@ -1015,6 +1017,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_SORT_MATCH_MIX: set_sort_mix(value); return 0;
         case GSR_TUNE_SORT_BALANCE: set_sort_balance(value); return 0;
         case GSR_TUNE_FUSED_DEPTH_HIST: g_fused_depth_hist = value ? 1 : 0; return 0;
+        case GSR_TUNE_PDL: g_pdl = value; return 0;
         case GSR_TUNE_FRAME_FORK: g_frame_fork = value ? 1 : 0; return 0;
         case GSR_TUNE_TILE: if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32"); h->tile_req = value; h->frame_valid = false; return 0;
         case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;

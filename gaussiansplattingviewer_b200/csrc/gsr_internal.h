@@ -64,6 +64,29 @@ struct SplatBuffers {
     uint32_t* depth_hist; // [4][256] digit counts of the depth keys, accumulated by k_preprocess (nullptr: not wanted)
 };
 
+// ---- programmatic dependent launch (sm_90+) ---------------------------------------------------------
+// A kernel launched with launch_pdl may become resident while the kernel in front of it on the stream is still
+// running; it must call pdl_wait() before it touches ANY global memory (the call returns when the kernel in
+// front has completed and its writes are visible; it is a no-op for a plain launch).  What this hides is the
+// launch latency and block scheduling of the next kernel behind the tail of the current one.
+extern int g_pdl;  // gsr_tune(GSR_TUNE_PDL): bit mask, see launch_pdl_m
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+inline void launch_pdl_m(int which, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = (g_pdl & which) ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 // ---- radix sort (radix_sort.cu) ----------------------------------------------------------------
 // Scratch for one sort: histograms for up to 8 passes, ticket counters, two look-back status buffers.
 struct SortScratch {

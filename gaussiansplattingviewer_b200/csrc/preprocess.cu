@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __rest
     // sort's histogram kernel (32 us over 3 M keys, bound by shared-memory atomics) is not launched
     __shared__ uint32_t s_dh[4 * 256];
     for (int i = threadIdx.x; i < 4 * 256; i += 256) s_dh[i] = 0;
+    pdl_wait();  // resident behind k_set_params: uniforms and cleared scratch are read after this
     unsigned n_culled = 0;
     if (threadIdx.x < 16) { P.view[threadIdx.x] = fp->view[threadIdx.x]; P.proj[threadIdx.x] = fp->proj[threadIdx.x]; }
     if (threadIdx.x == 32) {
@@ -713,11 +714,11 @@ void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers o
     const long long chunks = (n + 255) / 256;
     const unsigned grid = (unsigned)(chunks < 3LL * sm_count ? chunks : 3LL * sm_count);
     if (sh_dim == 48) {
-        if (dbg) k_preprocess<48, true><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
-        else k_preprocess<48, false><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        if (dbg) launch_pdl_m(8, k_preprocess<48, true>, dim3(grid), dim3(256), (size_t)smem, s, fp, scene, out, counters, (unsigned)n, sh_dim);
+        else launch_pdl_m(8, k_preprocess<48, false>, dim3(grid), dim3(256), (size_t)smem, s, fp, scene, out, counters, (unsigned)n, sh_dim);
     } else {
-        if (dbg) k_preprocess<0, true><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
-        else k_preprocess<0, false><<<grid, 256, smem, s>>>(fp, scene, out, counters, (unsigned)n, sh_dim);
+        if (dbg) launch_pdl_m(8, k_preprocess<0, true>, dim3(grid), dim3(256), (size_t)smem, s, fp, scene, out, counters, (unsigned)n, sh_dim);
+        else launch_pdl_m(8, k_preprocess<0, false>, dim3(grid), dim3(256), (size_t)smem, s, fp, scene, out, counters, (unsigned)n, sh_dim);
     }
 }
 

@@ -352,6 +352,7 @@ __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_pass2(const uint32_t* __re
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t mask = (1u << bits) - 1u;
     const uint32_t lt_mask = (1u << lane) - 1u;
+    pdl_wait();  // resident behind the previous pass; nothing of global memory is touched before this
     long long n = n_dev ? (long long)(*n_dev) : n_host;
     if (n > capacity) n = capacity;
 
@@ -628,13 +629,13 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
         if (pf_ctas > 0) {
             if constexpr (sizeof(KeyT) == 4) {
                 if (identity)
-                    k_rs_pass2<RS2_ITEMS, RS2_S, true><<<(unsigned)grid, RS_THREADS, RS2_SMEM, stream>>>(
-                        kin, kout, nullptr, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
-                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
+                    launch_pdl_m(1, k_rs_pass2<RS2_ITEMS, RS2_S, true>, dim3((unsigned)grid), dim3(RS_THREADS), RS2_SMEM, stream,
+                               kin, kout, (const uint32_t*)nullptr, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
+                               (const uint32_t*)(scratch->hist + p * 256), scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
                 else
-                    k_rs_pass2<RS2_ITEMS, RS2_S, false><<<(unsigned)grid, RS_THREADS, RS2_SMEM, stream>>>(
-                        kin, kout, vin, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
-                        scratch->hist + p * 256, scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
+                    launch_pdl_m(1, k_rs_pass2<RS2_ITEMS, RS2_S, false>, dim3((unsigned)grid), dim3(RS_THREADS), RS2_SMEM, stream,
+                               kin, kout, (const uint32_t*)vin, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
+                               (const uint32_t*)(scratch->hist + p * 256), scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
             }
         } else if (small)
             launch_pass<KeyT, RsCfg<KeyT>::SMALL>(identity, (unsigned)grid, stream, kin, kout, vin, vout, n_host, n_dev, capacity,
