@@ -308,6 +308,9 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
             launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges,
                              h->ss_i.hist, h->d_counters, sa);
             h->launches += 1;
+            // the frame's counters are final after the tile scan: their read-back runs here, beside the depth sort,
+            // not behind the blend kernel in front of the next frame
+            CK(cudaMemcpyAsync(h->h_counters, h->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, sa));
             CK(cudaEventRecord(h->ev_scan, sa));
             CK(cudaStreamWaitEvent(s, h->ev_cleared, 0));
         }
@@ -356,7 +359,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     launch_blend(h->d_fp, h->d_ranges, h->d_ivals[res], h->sp, out, fp.render_mod, fp.flags, h->tiles_x, h->tiles_y, s, tile);
     h->launches += 1;
     if (timed) cudaEventRecord(h->ev[6], s);
-    CK(cudaMemcpyAsync(h->h_counters, h->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, s));
+    if (!fork) CK(cudaMemcpyAsync(h->h_counters, h->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, s));
     h->last_result_buf = res;
     h->last_keys64 = keys64;
     h->frame_valid = true;
