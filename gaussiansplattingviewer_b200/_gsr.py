@@ -30,6 +30,7 @@ GSR_TUNE_TILE = 7
 GSR_TUNE_SORT_BALANCE = 8
 GSR_TUNE_FUSED_DEPTH_HIST = 9
 GSR_TUNE_PDL = 10
+GSR_TUNE_FUSED_RGB8 = 11
 
 
 class Stats(C.Structure):

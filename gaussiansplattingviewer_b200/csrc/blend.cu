@@ -86,7 +86,8 @@ template <int MODE, int PPT, bool COUNT, bool SHAPE8, int SKIP, int TILE = 16>  
 __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* __restrict__ fp, const int2* __restrict__ ranges,
                                                      const uint32_t* __restrict__ inst_gid, SplatBuffers sp,
                                                      float* __restrict__ out_rgba, unsigned flags,
-                                                     unsigned long long* __restrict__ pair_counts) {
+                                                     unsigned long long* __restrict__ pair_counts,
+                                                     uint8_t* __restrict__ out_rgb8) {
     constexpr int THREADS = TILE * TILE / PPT;
     constexpr int PER_THREAD = (BL_BATCH + THREADS - 1) / THREADS;  // records staged per thread per batch
     // one record = three consecutive float4 (48 B): the three shared-memory reads of a splat are constant
@@ -425,6 +426,47 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
             *o = make_float4(cr[k], cg[k], cb[k], (MODE == 5) ? 1.f : 1.f - T[k]);
         }
     }
+    // The capture loop wants the frame as RGB8 (main.py:852 glReadPixels): converted here with k_pack_rgb8's unorm8
+    // rule instead of by a second kernel that re-reads the float frame.  A full tile goes through shared memory
+    // (the record staging is free now) and leaves as aligned 32-bit words, 3 * TILE bytes per row; tiles cut by
+    // the image edge, or a width that is not a multiple of four, fall back to byte stores.
+    if (out_rgb8) {
+        const int x0 = blockIdx.x * TILE, y0 = blockIdx.y * TILE;
+        const bool full = ((W & 3) == 0) && (x0 + TILE <= W) && (y0 + TILE <= H);  // block-uniform
+        unsigned rgb[PPT];  // r | g << 8 | b << 16
+#pragma unroll
+        for (int k = 0; k < PPT; ++k) {
+            rgb[k] = (unsigned)__float2int_rn(fminf(fmaxf(cr[k], 0.f), 1.f) * 255.f) |
+                     ((unsigned)__float2int_rn(fminf(fmaxf(cg[k], 0.f), 1.f) * 255.f) << 8) |
+                     ((unsigned)__float2int_rn(fminf(fmaxf(cb[k], 0.f), 1.f) * 255.f) << 16);
+        }
+        if (full) {
+            __syncthreads();  // every thread is past its last read of the staged records
+            uint8_t* sb = reinterpret_cast<uint8_t*>(&s_rec[0][0][0]);  // [TILE rows (GL order)][3 * TILE]
+#pragma unroll
+            for (int k = 0; k < PPT; ++k) {
+                uint8_t* d = sb + ((lyb * PPT + k) * TILE + lx) * 3;
+                d[0] = (uint8_t)rgb[k]; d[1] = (uint8_t)(rgb[k] >> 8); d[2] = (uint8_t)(rgb[k] >> 16);
+            }
+            __syncthreads();
+            constexpr int WPR = 3 * TILE / 4;  // words per tile row
+            for (int w = threadIdx.x; w < TILE * WPR; w += THREADS) {
+                const int ly = w / WPR, j = w - ly * WPR;
+                const int row = (MODE == 5) ? (y0 + ly) : (H - 1 - (y0 + ly));
+                uint32_t* dst = reinterpret_cast<uint32_t*>(out_rgb8 + 3 * ((size_t)row * (size_t)W + x0)) + j;
+                *dst = reinterpret_cast<const uint32_t*>(sb)[ly * WPR + j];
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < PPT; ++k) {
+                if (!outside[k]) {
+                    const int row = (MODE == 5) ? (py0 + k) : (H - 1 - (py0 + k));
+                    uint8_t* d = out_rgb8 + 3 * ((size_t)row * (size_t)W + px);
+                    d[0] = (uint8_t)rgb[k]; d[1] = (uint8_t)(rgb[k] >> 8); d[2] = (uint8_t)(rgb[k] >> 16);
+                }
+            }
+        }
+    }
     if (COUNT) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -481,10 +523,10 @@ constexpr int BL_SKIP = 3;
 template <bool COUNT>
 static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                            float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
-                           unsigned long long* pc, cudaStream_t s, int tile) {
+                           unsigned long long* pc, cudaStream_t s, int tile, uint8_t* out_rgb8) {
     const dim3 grid((unsigned)tiles_x, (unsigned)tiles_y);
     constexpr int TH = 256 / BL_PPT;
-#define BL_ARGS fp, ranges, inst_gid, sp, out_rgba, flags, pc
+#define BL_ARGS fp, ranges, inst_gid, sp, out_rgba, flags, pc, out_rgb8
     if (tile == 32) {
         // 32x32 tiles (shader path only): a quarter of the tiles, less than half the instances to duplicate and
         // sort; the per-warp batch filter keeps the blend's work per pixel block what it was.  4 pixels per thread
@@ -524,15 +566,15 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
 }
 
 void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp, float* out_rgba,
-                  int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s, int tile) {
-    launch_blend_t<false>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, nullptr, s, tile);
+                  int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s, int tile, uint8_t* out_rgb8) {
+    launch_blend_t<false>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, nullptr, s, tile, out_rgb8);
 }
 
 // Instrumented variant: same image, plus pair_counts[0] += pairs visited, [1] += pairs that contributed.
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                         float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
                         unsigned long long* pair_counts, cudaStream_t s, int tile) {
-    launch_blend_t<true>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pair_counts, s, tile);
+    launch_blend_t<true>(fp, ranges, inst_gid, sp, out_rgba, render_mod, flags, tiles_x, tiles_y, pair_counts, s, tile, nullptr);
 }
 
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s) {

@@ -112,6 +112,7 @@ int g_pdl = 11;  // gsr_tune(GSR_TUNE_PDL): bit 0 radix passes, 1 duplicate, 2 b
 namespace {
 
 int g_fused_depth_hist = 1;  // gsr_tune(GSR_TUNE_FUSED_DEPTH_HIST): 0 = the depth sort runs its own histogram kernel
+int g_fused_rgb8 = 1;  // gsr_tune(GSR_TUNE_FUSED_RGB8): 0 = gsr_render_rgb8_host_async converts with k_pack_rgb8
 int g_frame_fork = 1;  // gsr_tune(GSR_TUNE_FRAME_FORK): 0 = every frame runs on one stream
 
 int free_gaussian_buffers(gsr_t* h) {
@@ -208,7 +209,8 @@ int tile_bits(int n_tiles) {
 // Enqueues one frame.  timed: record events between stages (h->ev[0..6]).
 // order_mode: 0 = sort this frame's depth keys; 1 = same, with keys for every Gaussian in front of the camera, and
 // remember the order; 2 = reuse the remembered order (same view-space depths: same view up to an in-plane shift)
-int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode = 0) {
+int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode = 0,
+                 uint8_t* out_rgb8 = nullptr) {
     FrameParams fp = fp_in;
     if (fp.flags & GSR_FLAG_KEYS64) {
         if (h->order_frozen) return fail(GSR_EINVAL, "a frozen order needs the two-level sort (clear GSR_FLAG_KEYS64)");
@@ -356,7 +358,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
         h->launches += 1;
     }
     if (timed) cudaEventRecord(h->ev[5], s);
-    launch_blend(h->d_fp, h->d_ranges, h->d_ivals[res], h->sp, out, fp.render_mod, fp.flags, h->tiles_x, h->tiles_y, s, tile);
+    launch_blend(h->d_fp, h->d_ranges, h->d_ivals[res], h->sp, out, fp.render_mod, fp.flags, h->tiles_x, h->tiles_y, s, tile, out_rgb8);
     h->launches += 1;
     if (timed) cudaEventRecord(h->ev[6], s);
     if (!fork) CK(cudaMemcpyAsync(h->h_counters, h->d_counters, sizeof(FrameCounters), cudaMemcpyDeviceToHost, s));
@@ -746,12 +748,14 @@ int gsr_render_rgb8_host_async(gsr_t* h, uint8_t* out, void* stream) {
     const int slot = (int)(h->async_idx++ & 1u);
     int rc = finish_slot(h, slot);
     if (rc) return rc;
-    rc = render_frame(h, h->fp, h->d_frame, s, false);
-    if (rc) return rc;
     const long long npx = (long long)h->W * h->H;
     uint8_t* dev = slot ? h->d_rgb8b : h->d_rgb8;
-    launch_pack_rgb8(h->d_frame, dev, npx, s);
-    h->launches += 1;
+    rc = render_frame(h, h->fp, h->d_frame, s, false, 0, g_fused_rgb8 ? dev : nullptr);  // the blend kernel packs RGB8 itself
+    if (rc) return rc;
+    if (!g_fused_rgb8) {
+        launch_pack_rgb8(h->d_frame, dev, npx, s);
+        h->launches += 1;
+    }
     CK(cudaEventRecord(h->ev_packed[slot], s));
     CK(cudaStreamWaitEvent(h->copy_stream, h->ev_packed[slot], 0));
     CK(cudaMemcpyAsync(out, dev, (size_t)npx * 3, cudaMemcpyDeviceToHost, h->copy_stream));
@@ -1021,6 +1025,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_SORT_BALANCE: set_sort_balance(value); return 0;
         case GSR_TUNE_FUSED_DEPTH_HIST: g_fused_depth_hist = value ? 1 : 0; return 0;
         case GSR_TUNE_PDL: g_pdl = value; return 0;
+        case GSR_TUNE_FUSED_RGB8: g_fused_rgb8 = value ? 1 : 0; return 0;
         case GSR_TUNE_FRAME_FORK: g_frame_fork = value ? 1 : 0; return 0;
         case GSR_TUNE_TILE: if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32"); h->tile_req = value; h->frame_valid = false; return 0;
         case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;

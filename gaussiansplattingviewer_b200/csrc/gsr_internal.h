@@ -150,7 +150,8 @@ template <typename KeyT>
 void launch_tile_ranges(const KeyT* sorted_keys, int key_shift, const FrameCounters* counters, long long capacity,
                         int2* ranges, int n_tiles, cudaStream_t s);
 void launch_blend(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
-                  float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s, int tile = 16);
+                  float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y, cudaStream_t s, int tile = 16,
+                  uint8_t* out_rgb8 = nullptr);  // out_rgb8: also write the frame as RGB8 (k_pack_rgb8's rule)
 void launch_pack_rgb8(const float* rgba, uint8_t* rgb, long long n_px, cudaStream_t s);
 void launch_extract_r(const float* rgba, float* r, long long n_px, cudaStream_t s);
 void launch_pack_disp_u16(const float* rgba, uint16_t* d, long long n_px, cudaStream_t s);

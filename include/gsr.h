@@ -224,6 +224,7 @@ int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* c
 #define GSR_TUNE_SORT_BALANCE 8 /* 1 (default) = radix passes cut the keys into equal spans, one or more per resident CTA; 0 = fixed 8192-key super-tiles */
 #define GSR_TUNE_FUSED_DEPTH_HIST 9 /* 1 (default) = the preprocess kernel counts the digits of the depth keys (no histogram kernel in the depth sort) */
 #define GSR_TUNE_PDL 10 /* bit mask of the kernels launched with programmatic dependent launch (resident behind their predecessor, griddepcontrol.wait before the first memory access): 1 radix passes, 2 duplicate, 4 blend, 8 preprocess; default 11, 0 = plain launches */
+#define GSR_TUNE_FUSED_RGB8 11 /* 1 (default) = gsr_render_rgb8_host_async lets the blend kernel write the RGB8 frame (no k_pack_rgb8 launch) */
 #define GSR_TUNE_BLEND_SKIP 3   /* 0 = none, 1 = warp vote per splat, 2 = warp filter per batch (quad vs the warp's pixel block), 3 (default) = 2 + alpha >= 1/255 reachable in the block */
 int gsr_tune(gsr_t* h, int key, int value);
 
