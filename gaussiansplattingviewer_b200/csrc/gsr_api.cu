@@ -790,11 +790,10 @@ int gsr_capture_stereo_async(gsr_t* h, const float view_left[16], const float ca
     memcpy(fp.campos, campos_left, 12);
     if (left_rgb) {
         fp.flags |= GSR_FLAG_CLAMP_UNORM;  // RGB8 FBO (main.py:846-852)
-        rc = render_frame(h, fp, h->d_frame, s, false, mode);
+        rc = render_frame(h, fp, h->d_frame, s, false, mode, g_fused_rgb8 ? d_left : nullptr);
         if (rc) return rc;
         if (mode) mode = 2;
-        launch_pack_rgb8(h->d_frame, d_left, (long long)npx, s);
-        h->launches += 1;
+        if (!g_fused_rgb8) { launch_pack_rgb8(h->d_frame, d_left, (long long)npx, s); h->launches += 1; }
     }
     if (disparity) {
         FrameParams fd = fp;
@@ -814,10 +813,9 @@ int gsr_capture_stereo_async(gsr_t* h, const float view_left[16], const float ca
         if (mode == 2) {  // the shared order needs equal depth rows; otherwise sort again
             for (int k = 8; k < 12; ++k) if (fr.view[k] != fp.view[k]) mode = 0;
         }
-        rc = render_frame(h, fr, h->d_frame, s, false, mode);
+        rc = render_frame(h, fr, h->d_frame, s, false, mode, g_fused_rgb8 ? d_right : nullptr);
         if (rc) return rc;
-        launch_pack_rgb8(h->d_frame, d_right, (long long)npx, s);
-        h->launches += 1;
+        if (!g_fused_rgb8) { launch_pack_rgb8(h->d_frame, d_right, (long long)npx, s); h->launches += 1; }
     }
     if (!h->order_frozen) h->order_buf = -1;
     CK(cudaEventRecord(h->ev_packed[slot], s));
