@@ -340,8 +340,14 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                 // than half of the four 8x8 warp blocks; testing them one by one cost 16 instructions per miss.
                 const int lane = threadIdx.x & 31;
                 constexpr int NW = BL_BATCH / 32;
-                uint32_t hits[NW];
-#pragma unroll
+                // The hits go to a per-warp list of record offsets in shared memory, in list order: walking it costs
+                // one LDS + pointer add per splat instead of find-first-set (BREV + FLO on the XU pipe, which the
+                // four ex2 of the body already load to 50 %), clear-lowest-bit and an index multiply.
+                uint16_t* hl = s_hit[threadIdx.x >> 5];
+                const unsigned rec_base = (unsigned)__cvta_generic_to_shared(&s_rec[buf][0][0]);  // < 64 K: fits 16 bits
+                const unsigned hl_base = (unsigned)__cvta_generic_to_shared(hl);
+                int n_hit_w = 0;
+#pragma unroll 4
                 for (int i = 0; i < NW; ++i) {
                     const int j = i * 32 + lane;
                     const float4 a = s_rec[buf][j][0];
@@ -375,19 +381,9 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                             keep = !(pmax < -theta - 0.05f);          // NaN anywhere keeps the splat
                         }
                     }
-                    hits[i] = __ballot_sync(0xffffffffu, keep);
-                }
-                // The hits go to a per-warp list of record offsets in shared memory, in list order: walking it costs
-                // one LDS + pointer add per splat instead of find-first-set (BREV + FLO on the XU pipe, which the
-                // four ex2 of the body already load to 50 %), clear-lowest-bit and an index multiply.
-                uint16_t* hl = s_hit[threadIdx.x >> 5];
-                const unsigned rec_base = (unsigned)__cvta_generic_to_shared(&s_rec[buf][0][0]);  // < 64 K: fits 16 bits
-                const unsigned hl_base = (unsigned)__cvta_generic_to_shared(hl);
-                int n_hit_w = 0;
-#pragma unroll
-                for (int i = 0; i < NW; ++i) {
-                    if ((hits[i] >> lane) & 1u) hl[n_hit_w + __popc(hits[i] & ((1u << lane) - 1u))] = (uint16_t)(rec_base + (i * 32 + lane) * 48);
-                    n_hit_w += __popc(hits[i]);
+                    const uint32_t hit = __ballot_sync(0xffffffffu, keep);
+                    if (keep) hl[n_hit_w + __popc(hit & ((1u << lane) - 1u))] = (uint16_t)(rec_base + j * 48);
+                    n_hit_w += __popc(hit);
                 }
                 __syncwarp();
                 for (int h0 = 0; h0 < n_hit_w; h0 += 8) {
