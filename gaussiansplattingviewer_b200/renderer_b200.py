@@ -291,9 +291,11 @@ class B200Renderer(GaussianRenderBase):
     def read_pixels_rgb8_async(self):
         """Pipelined capture loop (main.py:793-917 renders and reads back every pose): like read_pixels_rgb8,
         but returns at once; the copy to the host overlaps the next frame.  Returns the (H, W, 3) uint8 pinned
-        buffer the frame WILL land in: it is complete after the next-but-one call or after sync_host()."""
+        buffer the frame WILL land in: it is complete after the next-but-one call or after sync_host(), and it
+        is not written again before the call after that (three pinned buffers in rotation: the library waits for
+        the copy of call k when call k + 2 is made, and call k + 3 is the first to reuse call k's buffer)."""
         self._push_state()
-        k = self._async_k = getattr(self, "_async_k", 0) ^ 1
+        k = self._async_k = (getattr(self, "_async_k", -1) + 1) % 3
         buf = self._pinned_buf(("rgb8a", k), (self.h, self.w, 3), self._torch.uint8)
         _gsr.check(self._lib.gsr_render_rgb8_host_async(self._h, C.c_void_p(buf.data_ptr()), self._stream()))
         return buf.numpy()
@@ -303,12 +305,13 @@ class B200Renderer(GaussianRenderBase):
         at the left pose), right RGB8, packed on the device and copied to pinned host buffers while the next
         pose renders.  ``pose_*`` are the dicts ``colmap.load_camera_positions`` returns (keys camera_view,
         camera_position).  Returns {"left": (H,W,3) u8, "disparity": (H,W) u16, "right": (H,W,3) u8} views of
-        the buffers the images WILL land in: complete after the next-but-one call or ``sync_host()``."""
+        the buffers the images WILL land in: complete after the next-but-one call or ``sync_host()``, reused by
+        the call after that."""
         vl = _f32c(pose_left["camera_view"]).reshape(16)
         cl = _f32c(np.asarray(pose_left["camera_position"], dtype=np.float32)[:3])
         self._view, self._campos = vl.reshape(4, 4).copy(), cl.copy()  # update_camera_pose(poseLeft), main.py:848
         self._push_state()
-        k = self._cap_k = getattr(self, "_cap_k", 0) ^ 1
+        k = self._cap_k = (getattr(self, "_cap_k", -1) + 1) % 3  # three host buffers in rotation, see read_pixels_rgb8_async
         out = {}
         ptr = {"left": None, "disparity": None, "right": None}
         for name, shape, dt in (("left", (self.h, self.w, 3), self._torch.uint8),

@@ -454,3 +454,25 @@ def test_sort_balance_and_fused_histogram_knobs_change_nothing(R):
         for a, b in zip(out[0], o):
             assert np.array_equal(a, b)
     assert len(out[0][1]) > 0
+
+
+@pytest.mark.parametrize("W,H,tile", [(483, 271, 32), (484, 270, 16), (96, 64, 32), (50, 30, 32)])
+def test_rgb8_from_the_blend_kernel_matches_the_pack_kernel(R, W, H, tile):
+    """gsr_render_rgb8_host_async takes the RGB8 frame from the blend kernel's epilogue (aligned words out of
+    shared memory for full tiles, byte stores for tiles cut by the image edge or widths that are not a multiple
+    of four); the synchronous read-back converts the float frame with k_pack_rgb8.  Same bytes."""
+    g = scenes.synthetic_gaussians(30000, seed=33)
+    r, _ = _setup(R, g, W, H, debug=False)
+    r.tune(_gsr.GSR_TUNE_TILE, tile)
+    want = r.read_pixels_rgb8().copy()
+    got = r.read_pixels_rgb8_async()
+    r.sync_host()
+    assert want.shape == (H, W, 3) and want.max() > 0
+    assert np.array_equal(got, want)
+    r.tune(_gsr.GSR_TUNE_FUSED_RGB8, 0)
+    try:
+        got2 = r.read_pixels_rgb8_async()
+        r.sync_host()
+        assert np.array_equal(got2, want)
+    finally:
+        r.tune(_gsr.GSR_TUNE_FUSED_RGB8, 1)
