@@ -265,7 +265,6 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
                                                          FrameCounters* __restrict__ counters) {
     extern __shared__ int s_dyn[];
     __shared__ uint32_t s_hist[512];
-    __shared__ uint32_t s_wsum[TS_THREADS / 32 + 1];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int T = TX * TY;
     int* w = use_smem ? s_dyn : grid;
@@ -390,7 +389,6 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
         }
         counters->n_sort = overflow ? 0u : (unsigned)total;
     }
-    (void)s_wsum;
 }
 
 template <typename KeyT>
