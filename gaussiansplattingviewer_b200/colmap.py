@@ -7,8 +7,10 @@ and a RIGHT pose whose view matrix is the left one pre-multiplied by an x transl
 -0.5 in view space (:376-380), i.e. a camera 0.5 units to the right on the same image plane.
 
 The reference builds the view with ``glm.lookAtRH`` on ``glm.vec3`` (float32) inputs; PyGLM is not
-installed here, so ``util.look_at`` (glm's formula in float32) stands in: parity for this module is
-UNPINNED against a PyGLM run; the tests check it against the closed form instead.
+installed here, so ``util.look_at`` (glm's formula in float32) stands in.  Parity: the NumPy functions are
+pinned bit for bit to the reference's own code (tests/golden/make_colmap_golden.py cuts them out of main.py
+and runs them); ``load_camera_positions`` is pinned to the reference's call sequence run on a NumPy shim of
+GLM's float32 formulas (1 ulp), not to a PyGLM binary.
 
 Everything here is host-side NumPy: a few hundred 4x4 matrices per scene.  The arrays it returns feed
 ``B200Renderer.capture_stereo`` / ``draw_batch`` (C ABI: gsr_capture_stereo_async / gsr_render_batch).

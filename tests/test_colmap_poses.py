@@ -1,5 +1,7 @@
 """COLMAP images.txt / cameras.txt -> stereo pose batch (/root/reference/main.py:169-217,
-275-407, 602-632).  PyGLM is not installed, so these are closed-form checks (parity with a PyGLM run is unpinned)."""
+275-407, 602-632).  Closed-form checks plus tests/golden/colmap_ref.npz: the outputs of the reference's OWN
+functions (cut out of main.py's syntax tree by tests/golden/make_colmap_golden.py and executed unmodified; PyGLM is
+not installed, so its glm.* calls ran on a NumPy shim of GLM's float32 formulas)."""
 import numpy as np
 import pytest
 
@@ -72,3 +74,31 @@ def test_right_pose_is_half_a_unit_to_the_right_with_equal_depths(model):
         assert np.allclose(vr[i] @ np.append(cr[i], 1.0), [0, 0, 0, 1], atol=1e-5)
         p = np.array([0.3, -0.7, 1.9, 1.0], np.float32)
         assert (vl[i] @ p)[2] == (vr[i] @ p)[2]                                       # same view-space depth
+
+
+def test_pose_math_matches_the_reference_functions_run_here(golden):
+    """quaternion_to_rotation_matrix / create_look_at_from_colmap (main.py:167-217, pure NumPy): bit for bit.
+    load_camera_positions (main.py:275-407): the reference's call sequence on the glm shim, view matrices to 1 ulp
+    of their scale, the right camera position (glm.inverse there, -R^T t here) to 1e-6."""
+    z = golden("colmap_ref.npz")
+    rows = [str(r).split() for r in z["rows"]]
+    assert [r[0] for r in rows] == ["1", "2", "3"]
+    for i, e in enumerate(rows):
+        qw, qx, qy, qz = (float(e[k]) for k in (1, 2, 3, 4))
+        x, y, zz = (float(e[k]) for k in (5, 6, 7))
+        assert np.array_equal(colmap.quaternion_to_rotation_matrix(qw, qx, qy, qz), z[f"rotmat_{i}"])
+        pos, center, up = colmap.create_look_at_from_colmap(x, y, zz, qw, qx, qy, qz)
+        assert np.array_equal(pos, z[f"pos_{i}"]) and np.array_equal(center, z[f"center_{i}"])
+        assert np.array_equal(up, z[f"up_{i}"])
+        pl, pr = colmap.load_camera_positions(e)
+        assert np.array_equal(pl["camera_position"], z[f"campos_left_{i}"].astype(np.float32))
+        assert np.array_equal(pl["camera_front"], z[f"front_{i}"])
+        assert np.array_equal(pl["camera_up"], z[f"up_pose_{i}"].astype(np.float32))
+        for got, want in ((pl["camera_view"], z[f"view_left_{i}"]), (pr["camera_view"], z[f"view_right_{i}"])):
+            assert got.dtype == np.float32 and got.shape == (4, 4)
+            ulp = np.spacing(np.maximum(np.abs(want), np.float32(1.0)).astype(np.float32))
+            assert np.all(np.abs(got - want) <= ulp), (i, np.abs(got - want).max())
+        assert np.allclose(pr["camera_position"], z[f"campos_right_{i}"], rtol=0, atol=1e-6)
+        # the right view is the left one with x translation + baseline, bit for bit, also in the reference's result
+        assert np.array_equal(z[f"view_right_{i}"][1:], z[f"view_left_{i}"][1:])
+        assert z[f"view_right_{i}"][0, 3] == np.float32(z[f"view_left_{i}"][0, 3] + np.float32(-0.5))
