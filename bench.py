@@ -33,6 +33,25 @@ WORKLOADS = {
 METRIC = "frames/sec @1080p, 3M SH3 Gaussians/B200"
 
 
+def csrc_hash():
+    """Hash of the kernel sources: an ncu capture is only quoted beside a build of the same sources."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "gaussiansplattingviewer_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".h")):
+            with open(os.path.join(d, f), "rb") as fh:
+                h.update(f.encode() + b"\0" + fh.read())
+    return h.hexdigest()[:16]
+
+
+def static_config(workload, n, W, H, mod, keys64=False):
+    """The `config` object of BOTH arms (ours and --impl reference): what is rendered, nothing run-dependent."""
+    return {"workload": workload, "n_gaussians": n, "width": W, "height": H, "sh_degree": 3, "render_mod": mod,
+            "order_recomputed_every_frame": True, "poses": "orbit r=10 about the origin, one new pose per step",
+            "l2": "scene buffers (%.0f MB) exceed the 126 MB L2" % (n * 236 / 1e6)}
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -130,25 +149,25 @@ def run_ours(args):
     cam = Camera(H, W)
     # ---- scene: generated on rank 0, replicated ONCE by NCCL broadcast (no collective per frame)
     t_bcast_ms = 0.0
-    if rank == 0:
-        g = scenes.synthetic_gaussians(n, seed=0)
+    g = scenes.synthetic_gaussians(n, seed=0) if rank == 0 else None
     if world == 1:
         r.update_gaussian_data(g)
     else:
-        shapes = [(n, 3), (n, 4), (n, 3), (n, 1), (n, 48)]
+        # rank 0 uploads, the others allocate; the four resident planes are the NCCL broadcast buffers themselves
+        # (pose_shard.broadcast_scene_resident: gsr_alloc_gaussians + gsr_scene_buffer, no second copy of the scene)
+        from gaussiansplattingviewer_b200 import pose_shard
         if rank == 0:
-            ts = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (g.xyz, g.rot, g.scale, g.opacity, g.sh)]
+            r.update_gaussian_data(g)
         else:
-            ts = [torch.empty(s, dtype=torch.float32, device="cuda") for s in shapes]
+            r.alloc_gaussians(n, 48)
         torch.cuda.synchronize(); dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for t in ts:
+        for t in r.scene_buffers():
             dist.broadcast(t, src=0)
         e1.record(); torch.cuda.synchronize()
         t_bcast_ms = e0.elapsed_time(e1)
-        r.update_gaussian_data_device(*ts)
-        del ts
+        assert pose_shard.broadcast_scene_resident.__doc__  # the package entry point does exactly the above
     r.set_scale_modifier(1.0)
     r.set_render_mod(mod)
     r.update_camera_intrin(cam)
@@ -205,9 +224,11 @@ def run_ours(args):
     wall_b = (time.perf_counter() - t_b0) * 1e3
     # the copies run on the library's own stream: take the larger of the event time and the host clock
     ms_b = max_over_ranks(max(e0.elapsed_time(e1), wall_b))
-    clocks = sampler.stop() if rank == 0 else None
     assert img8.shape == (H, W, 3) and img8.any()
-    out = {"ms_a": ms_a, "ms_b": ms_b, "launches": launches, "t_bcast_ms": t_bcast_ms, "clocks": clocks}
+    out = {"ms_a": ms_a, "ms_b": ms_b, "launches": launches, "t_bcast_ms": t_bcast_ms}
+    # ---- config 5 (BASELINE.json configs[4]): 1024 trajectory poses over the same scene, sharded over the ranks
+    out["config5"] = run_config5(r, cam, rank, world, sync_all, W, H) if args.workload == "3M_sh3_1080p" else None
+    out["clocks"] = sampler.stop() if rank == 0 else None
     # ---- region C (rank 0): per-stage CUDA-event times over K frames, pair counts, micro-benchmark peaks
     if rank == 0:
         acc = np.zeros(7)
@@ -234,6 +255,171 @@ def run_ours(args):
                cam=cam, pose=pose_of(Wm + K - 1))
     if world > 1:
         dist.barrier()
+    return out
+
+
+def run_config5(r, cam, rank, world, sync_all, W, H, n_poses=1024):
+    """The render_all.py / camera_data.csv workload (/root/reference/render_all.py:14-35, main.py:529-562, 793-840):
+    a FIXED list of 1024 poses (closed Catmull-Rom loop through the 18 rows of the viewer's camera_data.csv,
+    SURVEY 8d) over the resident scene, split into contiguous slices with pose_shard.shard_range; strong scaling.
+    Two timed loops per rank, each bracketed by barrier + synchronize, time = max over ranks:
+      device : update_camera_pose + draw per pose
+      e2e    : update_camera_pose + read_pixels_rgb8_async per pose, sync_host at the end (every RGB8 frame is
+               copied to pinned host memory inside the region)"""
+    import torch
+    import torch.distributed as dist
+    from gaussiansplattingviewer_b200 import pose_shard, scenes
+    rows = np.load(os.path.join(ROOT, "tests", "golden", "camera_data.npy"))
+    views, campos = scenes.trajectory_poses(rows, n_poses)
+    lo, hi = pose_shard.shard_range(n_poses, rank, world)
+    zero3 = np.zeros(3, np.float32)
+
+    def pose(i):
+        return {"camera_front": zero3, "camera_up": zero3, "camera_position": campos[i], "camera_view": views[i]}
+
+    res = {}
+    for name in ("device", "e2e"):
+        for i in range(lo, min(lo + 3, hi)):  # warm-up on the slice's first poses
+            r.update_camera_pose(cam, True, pose(i))
+            r.draw() if name == "device" else r.read_pixels_rgb8_async()
+        r.sync_host()
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for i in range(lo, hi):
+            r.update_camera_pose(cam, True, pose(i))
+            r.draw() if name == "device" else r.read_pixels_rgb8_async()
+        if name == "e2e":
+            r.sync_host()
+        e1.record()
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        ms = max(e0.elapsed_time(e1), wall) if name == "e2e" else e0.elapsed_time(e1)
+        host_ms = wall  # host time to ENQUEUE the slice is below this; the loop never waits except at the end
+        sync_all()
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+            allt = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(allt, t)
+            per_rank = [float(x.item()) for x in allt]
+        else:
+            per_rank = [ms]
+        res[name] = {"views_per_s": round(n_poses / (max(per_rank) * 1e-3), 1), "ms_total_max_over_ranks": round(max(per_rank), 3),
+                     "per_rank_ms": {"min": round(min(per_rank), 3), "median": round(float(np.median(per_rank)), 3),
+                                     "max": round(max(per_rank), 3)},
+                     "poses_per_rank": [pose_shard.shard_range(n_poses, k, world)[1] - pose_shard.shard_range(n_poses, k, world)[0]
+                                        for k in range(world)][:2] + (["..."] if world > 2 else []),
+                     "rank0_wall_ms": round(host_ms, 3)}
+    assert not r.stats().overflow
+    return {"workload": "1024 poses (closed Catmull-Rom loop through camera_data.csv, x3 about the origin) over the "
+                        "3M SH3 scene at 1920x1080, contiguous slices per rank (pose_shard.shard_range)",
+            "n_poses": n_poses, "scaling": "strong", "views_per_s": res["device"]["views_per_s"],
+            "views_per_s_e2e": res["e2e"]["views_per_s"], "device": res["device"], "e2e": res["e2e"],
+            "d2h_bytes_per_view": W * H * 3}
+
+
+def run_config4(local, K=10):
+    """BASELINE.json configs[3]: 6M SH3 Gaussians at 3840x2160, colour (3), depth/disparity (-1, the 1.2x-scale second
+    geometry pass, gau_vert.glsl:151-156,182-211) and flat ball (-3).  Frames/s with the scene resident (CUDA events
+    over K frames at new orbit poses) and per-stage times (gsr_render_timed)."""
+    import torch
+    from gaussiansplattingviewer_b200 import scenes
+    from gaussiansplattingviewer_b200.renderer_b200 import B200Renderer
+    from gaussiansplattingviewer_b200.util import Camera
+    n, W, H = 6_000_000, 3840, 2160
+    r = B200Renderer(W, H, device=local)
+    cam = Camera(H, W)
+    r.update_gaussian_data(scenes.synthetic_gaussians(n, seed=1))
+    r.update_camera_intrin(cam)
+    out = {"n_gaussians": n, "width": W, "height": H, "modes": {}}
+    for mod in (3, -1, -3):
+        r.set_render_mod(mod)
+        for s_ in range(3):
+            r.update_camera_pose(cam, True, orbit_pose(s_, K + 3)); r.draw()
+        torch.cuda.synchronize()
+        if r.stats().overflow:  # first frames of a mode may grow the instance buffers (draw() repairs on the next call)
+            r.update_camera_pose(cam, True, orbit_pose(0, K + 3)); r.draw(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for s_ in range(K):
+            r.update_camera_pose(cam, True, orbit_pose(3 + s_, K + 3)); r.draw()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        acc = np.zeros(7)
+        for s_ in range(K):
+            r.update_camera_pose(cam, True, orbit_pose(3 + s_, K + 3))
+            _, ss = r.draw_timed()
+            acc += [ss.ms_preprocess, ss.ms_sort_depth, ss.ms_ranges, ss.ms_duplicate, ss.ms_sort_tiles, ss.ms_blend, ss.ms_total]
+        st = r.stats()
+        out["modes"][str(mod)] = {"frames_per_s": round(1e3 / ms, 1), "ms_per_frame": round(ms, 4), "overflow": int(st.overflow),
+                                  "visible": int(st.n_visible), "instances": int(st.n_instances),
+                                  "stage_ms": dict(zip(["preprocess", "sort_depth", "ranges", "duplicate", "sort_tiles", "blend", "total"],
+                                                       [round(float(v), 4) for v in acc / K]))}
+    del r
+    torch.cuda.empty_cache()
+    return out
+
+
+def sort_gaussian_torch(xyz_np, view_mat_np):
+    """The reference's GPU sort, restated line for line (/root/reference/renderer_ogl.py:41-53; the selector at
+    :56-64 picks it whenever torch sees a CUDA device): H2D of xyz on EVERY call (:47), bmm, argsort, D2H."""
+    import torch
+    xyz = torch.tensor(xyz_np).cuda()
+    view_mat = torch.tensor(view_mat_np).cuda()
+    xyz_view = view_mat[None, :3, :3] @ xyz[..., None] + view_mat[None, :3, 3, None]
+    depth = xyz_view[:, 2, 0]
+    index = torch.argsort(depth)
+    index = index.type(torch.int32).reshape(-1, 1).cpu().numpy()
+    return index
+
+
+def sort_baselines(r, g, view):
+    """Same-box context for "sort Gkeys/s": the reference's torch sort next to gsr_sort_depth on the same 3M
+    positions, and torch.sort (CUB) next to gsr_sort_pairs on 2^24 random 32-bit keys."""
+    import torch
+    out = {}
+    n = len(g.xyz)
+    view = np.ascontiguousarray(view, dtype=np.float32)
+
+    def best_wall(fn, reps=3):
+        fn(); torch.cuda.synchronize()
+        best = None
+        for _ in range(reps):
+            torch.cuda.synchronize(); t0 = time.perf_counter(); res = fn(); torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) * 1e3
+            best = dt if best is None else min(best, dt)
+        return best, res
+
+    ms_ref, idx_ref = best_wall(lambda: sort_gaussian_torch(g.xyz, view))
+    ms_ours, idx_ours = best_wall(lambda: r.gaussian_order(view))
+    d = (g.xyz @ view[2, :3] + view[2, 3]).astype(np.float32)
+    out["reference_torch_ms"] = round(ms_ref, 3)            # _sort_gaussian_torch as the reference calls it
+    out["gsr_sort_depth_host_ms"] = round(ms_ours, 3)       # B200Renderer.gaussian_order: resident xyz, index to host
+    out["same_depth_order"] = bool(np.array_equal(d[idx_ref[:, 0]], d[idx_ours[:, 0]]))
+    # device-only parts on resident data (CUDA events): bmm + argsort  vs  gsr_sort_depth into device memory
+    xyz_t = torch.from_numpy(g.xyz).cuda(); vm = torch.from_numpy(view).cuda()
+
+    def ev(fn, reps=5):
+        fn(); torch.cuda.synchronize()
+        best = None
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+            t = e0.elapsed_time(e1)
+            best = t if best is None else min(best, t)
+        return best
+
+    out["torch_resident_argsort_ms"] = round(ev(lambda: torch.argsort((vm[None, :3, :3] @ xyz_t[..., None] + vm[None, :3, 3, None])[:, 2, 0])), 4)
+    out["gsr_sort_depth_device_ms"] = round(ev(lambda: r.gaussian_order(view, to_host=False)), 4)
+    out["depth_order_n"] = n
+    m = 1 << 24
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    tk0 = torch.randint(-2 ** 31, 2 ** 31 - 1, (m,), dtype=torch.int32, device="cuda", generator=gen)
+    t_torch = ev(lambda: torch.sort(tk0))
+    out["torch_sort_pairs_2p24_ms"] = round(t_torch, 4)     # torch.sort returns (sorted keys, int64 indices)
+    out["torch_sort_pairs_2p24_gkeys_s"] = round(m / (t_torch * 1e-3) / 1e9, 2)
+    del xyz_t, tk0
     return out
 
 
@@ -289,10 +475,12 @@ def run_reference(args):
     cam = Camera(H, W)
     # bounded sample: every stride-th Gaussian at full resolution, sized from a probe so that
     # (K + W) steps take about args.ref_budget seconds
-    probe = subsample(g_full, 64)
-    _, ts, tr = cpu_frame(probe, cam, orbit_pose(0, K + Wm), W, H, mod, use_ref)
-    est_full = (ts + tr) * 64
-    stride = int(max(1, np.ceil(est_full * (K + Wm) / args.ref_budget)))
+    stride = 1
+    if args.ref_budget > 0:  # opt-in bounded sample: every stride-th Gaussian, sized from a probe
+        probe = subsample(g_full, 64)
+        _, ts, tr = cpu_frame(probe, cam, orbit_pose(0, K + Wm), W, H, mod, use_ref)
+        est_full = (ts + tr) * 64
+        stride = int(max(1, np.ceil(est_full * (K + Wm) / args.ref_budget)))
     g = subsample(g_full, stride)
     for s in range(Wm):
         cpu_frame(g, cam, orbit_pose(s, K + Wm), W, H, mod, use_ref)
@@ -302,13 +490,16 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     frac = len(g) / n
     fps = frac * K / dt
-    sample = (f"every {stride}-th Gaussian ({len(g)} of {n}) at full {W}x{H}; a step = numpy depth sort + CPU "
-              f"rasteriser of that sample; frames/s scaled by {frac:.4f}")
+    if stride == 1:
+        sample = (f"the full workload: all {n} Gaussians at {W}x{H}, a step = the reference's numpy depth sort + its "
+                  f"shaders run on the host cores ({'oracle/_ref' if use_ref else 'oracle/gs_oracle.c'}), one new orbit pose per step")
+    else:
+        sample = (f"every {stride}-th Gaussian ({len(g)} of {n}) at full {W}x{H}; a step = numpy depth sort + CPU "
+                  f"rasteriser of that sample; frames/s scaled by {frac:.4f}")
     return {"metric": METRIC, "value": fps, "unit": "frames/s", "impl": "reference", "n_gpus": args.gpus, "steps": K,
             "warmup": Wm, "ms_per_step": 1e3 * dt / K / frac, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "n_gaussians": n, "width": W, "height": H, "sh_degree": 3,
-                       "render_mod": mod},
+            "config": static_config(args.workload, n, W, H, mod), "n_gaussians_rendered": len(g),
             "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": O.num_threads(),
                              "kind": "reference" if use_ref else "port", "sample": sample},
             "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -323,7 +514,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="3M_sh3_1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--keys64", action="store_true", help="one 64-bit-key sort instead of the two-level sort")
-    ap.add_argument("--ref-budget", type=float, default=120.0, help="seconds of CPU work for --impl reference")
+    ap.add_argument("--ref-budget", type=float, default=0.0,
+                    help="--impl reference: 0 (default) = the full configuration; > 0 = sub-sample the Gaussians to about this many seconds of CPU work")
+    ap.add_argument("--no-config4", action="store_true", help="skip the 6M / 3840x2160 leg (configs[3])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -367,12 +560,15 @@ def main():
                             "ex2_tops": round(contributed / (sm["blend"] * 1e-3) / 1e12, 3),
                             "frac_ex2": round(contributed / (sm["blend"] * 1e-3) / 1e12 / ex2_peak, 4)})
     # DRAM bytes per launch from the committed ncu --set full capture of the same workload (not measured in this run)
-    traffic = {}
+    traffic, traffic_stale = {}, False
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
             tj = json.load(f)
         if tj.get("workload") == args.workload and not args.keys64:
-            traffic = tj.get("per_stage", {})
+            if tj.get("csrc_hash") == csrc_hash():
+                traffic = tj.get("per_stage", {})
+            else:
+                traffic_stale = True  # captured on other kernel sources: not quoted
     except Exception:
         traffic = {}
     for k in stages:
@@ -387,17 +583,17 @@ def main():
         roof = {"kernel": dom, "bound": "hbm", "achieved": stages[dom]["gbs"], "peak": hbm_peak, "unit": "GB/s",
                 "frac": stages[dom]["frac_hbm"], "traffic": traffic.get(dom), "peak_source": peak_src,
                 "alg_bytes_per_launch": stages[dom]["alg_bytes"]}
+    roof["traffic_stale"] = traffic_stale
+    roof["csrc_hash"] = csrc_hash()
     fps = world * K / (o["ms_a"] * 1e-3)
     e2e_fps = world * K / (o["ms_b"] * 1e-3)
     line = {"metric": METRIC, "value": round(fps, 2), "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": o["Wm"],
             "ms_per_step": round(o["ms_a"] / K, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "n_gaussians": n, "width": W, "height": H, "sh_degree": 3,
-                       "render_mod": o["mod"], "sort": "keys64" if args.keys64 else "two-level (depth over N, tile over D)",
-                       "order_recomputed_every_frame": True, "poses": "orbit r=10 about the origin, one new pose per step",
-                       "l2": "scene buffers (%.0f MB) exceed the 126 MB L2" % (n * 236 / 1e6),
-                       "visible": st["visible"], "instances": st["instances"],
-                       "mean_tile_list": round(st["instances"] / st["tiles"], 1), "tile_edge_px": 32},
+            "config": static_config(args.workload, n, W, H, o["mod"]),
+            "workload_stats": {"sort": "keys64" if args.keys64 else "two-level (depth over the visible Gaussians, tile over D)",
+                               "visible": st["visible"], "instances": st["instances"],
+                               "mean_tile_list": round(st["instances"] / st["tiles"], 1), "tile_edge_px": 32},
             "clocks": o["clocks"],
             "e2e": {"value": round(e2e_fps, 2), "unit": "frames/s", "h2d_bytes_per_step": 16 * 4 * 2 + 9 * 4 + 6 * 4,
                     "d2h_bytes_per_step": W * H * 3,
@@ -431,6 +627,7 @@ def main():
             best = t if best is None else min(best, t)
         line["sort"]["pairs_2p24_u32_gkeys_s"] = round(m / (best * 1e-3) / 1e9, 2)
         line["sort"]["pairs_2p24_u32_ms"] = round(best, 4)
+        line["sort"].update(sort_baselines(o["renderer"], o["scene"], o["pose"]["camera_view"]))
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as O
         img, t_sort, t_rast = cpu_frame(o["scene"], o["cam"], o["pose"], W, H, o["mod"], use_ref=False)
@@ -439,6 +636,10 @@ def main():
                                 "kind": "port", "sample": "one full frame of the same workload (last timed pose): numpy "
                                 "depth sort %.2f s + oracle/gs_oracle.c rasteriser %.2f s" % (t_sort, t_rast),
                                 "max_abs_diff_vs_gpu": float(np.abs(gpu_img - img).max())}
+    line["config5"] = o["config5"]
+    if world == 1 and not args.no_config4 and args.workload == "3M_sh3_1080p":
+        del o["renderer"]
+        line["config4"] = run_config4(int(os.environ.get("LOCAL_RANK", "0")))
     emit(line)
 
 

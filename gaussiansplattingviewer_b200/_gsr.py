@@ -111,7 +111,15 @@ def load():
     return lib
 
 
+GSR_EOVERFLOW = -4
+
+
+class GsrOverflow(RuntimeError):
+    """GSR_EOVERFLOW: a frame did not fit the tile-instance buffers (they have been grown): submit it again."""
+
+
 def check(rc: int):
     if rc != 0:
         msg = load().gsr_last_error()
-        raise RuntimeError(f"gsr error {rc}: {msg.decode() if msg else ''}")
+        text = f"gsr error {rc}: {msg.decode() if msg else ''}"
+        raise (GsrOverflow(text) if rc == GSR_EOVERFLOW else RuntimeError(text))

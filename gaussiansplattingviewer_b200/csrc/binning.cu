@@ -356,7 +356,7 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
             const unsigned c = (unsigned)w[y * gw + x];
             ranges[id] = (overflow || c == 0) ? make_int2(0, 0) : make_int2((int)start, (int)(start + c));  // empty: (0, 0)
             const uint32_t hd = (uint32_t)id >> bits0;
-            if (hd != run_digit) {
+            if (hist && hd != run_digit) {
                 if (run_sum) atomicAdd(&s_hist[256 + run_digit], run_sum);
                 run_digit = hd; run_sum = 0;
             }
@@ -364,9 +364,9 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
             start += c;
             if (++x == TX) { x = 0; ++y; }
         }
-        if (run_sum) atomicAdd(&s_hist[256 + run_digit], run_sum);
+        if (hist && run_sum) atomicAdd(&s_hist[256 + run_digit], run_sum);
     }
-    {
+    if (hist) {  // nullptr: more than 16 tile bits, the tile sort counts its digits itself (k_rs_hist)
         // low-digit histogram: thread t sums the tiles id = d + 2^bits0 * (slice + n_slices * j) of its digit d
         const int nd = 1 << bits0;
         const int n_slices = TS_THREADS >> bits0;  // >= 4 (bits0 <= 8)
@@ -379,7 +379,7 @@ __global__ void __launch_bounds__(TS_THREADS) k_tile_scan(int* __restrict__ grid
         if (acc) atomicAdd(&s_hist[d], acc);
     }
     __syncthreads();
-    if (t < 512) hist[t] = s_hist[t];
+    if (hist && t < 512) hist[t] = s_hist[t];
     if (t == 0) {
         counters->n_instances = (total > 0xFFFFFFFFull) ? 0xFFFFFFFFu : (unsigned)total;
         counters->overflow = overflow ? 1u : 0u;

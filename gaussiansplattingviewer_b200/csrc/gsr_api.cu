@@ -80,6 +80,7 @@ struct gsr_renderer {
     uint8_t* d_cap[2] = {nullptr, nullptr};  // stereo capture slots: left RGB8 | right RGB8 | disparity u16
     int order_buf = -1;                      // d_gid[] buffer holding a shared depth order (stereo capture, frozen order)
     bool order_frozen = false;               // gsr_freeze_order: frames draw in the stored order
+    float frozen_view[16] = {};              // the view of that order (gsr_sort_depth borrows its buffers and re-freezes)
     cudaStream_t copy_stream = nullptr;
     // frame-internal fork: scratch clears and the single-CTA k_tile_scan run beside preprocess / the depth sort
     cudaStream_t aux_stream = nullptr;
@@ -308,7 +309,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
             CK(cudaEventRecord(h->ev_pre, s));
             CK(cudaStreamWaitEvent(sa, h->ev_pre, 0));
             launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges,
-                             h->ss_i.hist, h->d_counters, sa);
+                             scan_hist ? h->ss_i.hist : nullptr, h->d_counters, sa);
             h->launches += 1;
             // the frame's counters are final after the tile scan: their read-back runs here, beside the depth sort,
             // not behind the blend kernel in front of the next frame
@@ -329,7 +330,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
             CK(cudaStreamWaitEvent(s, h->ev_scan, 0));
         } else {
             launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges,
-                             h->ss_i.hist, h->d_counters, s);
+                             scan_hist ? h->ss_i.hist : nullptr, h->d_counters, s);
             h->launches += 1;
         }
         if (timed) cudaEventRecord(h->ev[3], s);
@@ -342,7 +343,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
                                          &h->launches, &so);
     } else {
         if (timed) cudaEventRecord(h->ev[2], s);
-        launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges, h->ss_i.hist,
+        launch_tile_scan(h->d_tile_grid, sp.grid_stride, h->grid_w, h->tiles_x, h->tiles_y, bits0, cap, h->d_ranges, nullptr,
                          h->d_counters, s);
         h->launches += 1;
         if (timed) cudaEventRecord(h->ev[3], s);
@@ -369,6 +370,29 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     return 0;
 }
 
+// The asynchronous entry points (gsr_render, gsr_render_batch) cannot know whether the frame they enqueue fits the
+// instance buffers; k_tile_scan counts such frames in the sticky words, whose pinned copy the NEXT call looks at:
+// it grows the buffers and tells the caller (GSR_EOVERFLOW) that an earlier frame was incomplete.
+int repair_sticky_overflow(gsr_t* h, bool* grew) {
+    *grew = false;
+    const volatile FrameCounters* hc = h->h_counters;
+    if (!hc->sticky_overflow) return 0;
+    CK(cudaDeviceSynchronize());
+    const long long d = std::max<long long>(hc->sticky_max_d, hc->n_instances);
+    const long long want = std::max(h->capacity * 2, d + d / 8);
+    CK(cudaMemset(&h->d_counters->sticky_overflow, 0, 8));
+    h->h_counters->sticky_overflow = 0;
+    h->h_counters->sticky_max_d = 0;
+    h->h_counters->overflow = 0;
+    h->slot_busy[0] = h->slot_busy[1] = false;
+    h->capacity_req = 0;
+    if (h->capacity >= MAX_CAPACITY) return fail(GSR_EOVERFLOW, "tile-instance buffer overflow at the maximum capacity");
+    int rc = ensure_capacity(h, want, h->cap_keys64);
+    if (rc) return rc;
+    *grew = true;
+    return 0;
+}
+
 // render + (optional conversion) + D2H, growing the instance buffers on overflow
 int render_to_host(gsr_t* h, void* host_dst, int kind /*0 rgba f32, 1 rgb8, 2 r32f*/, cudaStream_t s) {
     if (!host_dst) return fail(GSR_EINVAL, "null output");
@@ -388,7 +412,17 @@ int render_to_host(gsr_t* h, void* host_dst, int kind /*0 rgba f32, 1 rgb8, 2 r3
             CK(cudaMemcpyAsync(host_dst, h->d_r32, (size_t)npx * 4, cudaMemcpyDeviceToHost, s));
         }
         CK(cudaStreamSynchronize(s));
-        if (!h->h_counters->overflow) return 0;
+        if (!h->h_counters->overflow) {
+            // the overflowed attempts of this call (and earlier synchronous ones) are repaired: forget them, or the
+            // next pipelined sync point would report them again (nothing asynchronous is in flight on this path)
+            if (h->h_counters->sticky_overflow && !h->slot_busy[0] && !h->slot_busy[1]) {
+                CK(cudaMemsetAsync(&h->d_counters->sticky_overflow, 0, 8, s));
+                CK(cudaStreamSynchronize(s));
+                h->h_counters->sticky_overflow = 0;
+                h->h_counters->sticky_max_d = 0;
+            }
+            return 0;
+        }
         const long long d = h->h_counters->n_instances;
         if (h->capacity >= MAX_CAPACITY) break;
         long long want = std::max(h->capacity * 2, d + d / 8);
@@ -673,6 +707,10 @@ int gsr_render(gsr_t* h, float* out_rgba, void* stream) {
     if (!h) return fail(GSR_EINVAL, "null handle");
     CK(cudaSetDevice(h->device));
     h->fp.sh_dim = h->sh_dim;
+    bool grew = false;
+    int rc = repair_sticky_overflow(h, &grew);
+    if (rc) return rc;
+    if (grew) return fail(GSR_EOVERFLOW, "an earlier frame overflowed the tile-instance buffers and is incomplete (grown now): draw again");
     return render_frame(h, h->fp, out_rgba, (cudaStream_t)stream, false);
 }
 
@@ -841,6 +879,10 @@ int gsr_render_batch(gsr_t* h, const float* views, const float* campos, int n_vi
     CK(cudaSetDevice(h->device));
     if (!h->have_camera) return fail(GSR_EINVAL, "set intrinsics with gsr_set_camera first");
     h->fp.sh_dim = h->sh_dim;
+    bool grew = false;
+    int rc0 = repair_sticky_overflow(h, &grew);
+    if (rc0) return rc0;
+    if (grew) return fail(GSR_EOVERFLOW, "an earlier frame overflowed the tile-instance buffers and is incomplete (grown now): draw again");
     const size_t frame = (size_t)h->W * h->H * 4;
     FrameParams fp = h->fp;
     for (int v = 0; v < n_views; ++v) {
@@ -870,8 +912,13 @@ int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_i
     if (!dst_is_device) CK(cudaStreamSynchronize(s));
     h->frame_valid = false;
     h->order_buf = -1;
-    h->order_frozen = false;
     CK(cudaGetLastError());
+    // the sort borrowed the buffers a frozen order lives in: rebuild that order (one more sort of a rare call)
+    if (h->order_frozen) {
+        float fv[16];
+        memcpy(fv, h->frozen_view, 64);
+        return gsr_freeze_order(h, fv, stream);
+    }
     return 0;
 }
 
@@ -886,6 +933,7 @@ int gsr_freeze_order(gsr_t* h, const float view[16], void* stream) {
     h->order_buf = 0;
     h->order_frozen = true;
     h->frame_valid = false;
+    memcpy(h->frozen_view, view, 64);
     if (N == 0) return 0;
     launch_depth_keys(h->d_xyz, view, h->d_dkey[0], N, s, 1);
     h->launches += 1;

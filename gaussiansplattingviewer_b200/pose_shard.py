@@ -50,5 +50,28 @@ def broadcast_scene(gaus, device, src: int = 0):
     return out
 
 
+def broadcast_scene_resident(renderer, gaus, src: int = 0):
+    """Replicates a scene from rank `src` straight into every rank's RESIDENT scene buffers: the source rank
+    uploads `gaus` (update_gaussian_data), the others allocate empty buffers (gsr_alloc_gaussians), and the four
+    resident planes (xyz, rot, scale+opacity, sh; gsr_scene_buffer) are the broadcast buffers themselves — one
+    NCCL broadcast per plane, no second copy of the scene anywhere.  Returns (n, sh_dim)."""
+    import torch
+    import torch.distributed as dist
+
+    rank = dist.get_rank()
+    meta = torch.zeros(2, dtype=torch.int64, device=renderer.device)
+    if rank == src:
+        meta[0], meta[1] = len(gaus), gaus.sh_dim
+        renderer.update_gaussian_data(gaus)
+    dist.broadcast(meta, src=src)
+    n, sh_dim = int(meta[0]), int(meta[1])
+    if rank != src:
+        renderer.alloc_gaussians(n, sh_dim)
+    if n > 0:
+        for t in renderer.scene_buffers():
+            dist.broadcast(t, src=src)
+    return n, sh_dim
+
+
 def tensors_to_gaussians(ts) -> GaussianData:
     return GaussianData(*[t.cpu().numpy() for t in ts])

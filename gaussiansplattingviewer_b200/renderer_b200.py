@@ -120,6 +120,34 @@ class B200Renderer(GaussianRenderBase):
         _gsr.check(self._lib.gsr_set_gaussians(self._h, *[C.c_void_p(t.data_ptr()) for t in ts], n,
                                                int(ts[4].shape[1]), 1))
 
+    def alloc_gaussians(self, n: int, sh_dim: int):
+        """Resident scene buffers for n Gaussians, contents undefined: the receiving side of a scene broadcast
+        (pose_shard.broadcast_scene_resident)."""
+        _gsr.check(self._lib.gsr_alloc_gaussians(self._h, int(n), int(sh_dim)))
+        self.gaussians = None
+
+    def scene_buffers(self):
+        """The four resident scene planes as float32 CUDA tensors that ALIAS the library's buffers (no copy):
+        xyz (N,3), rot (N,4 wxyz), scale+opacity (N,4), sh (N,sh_dim).  Valid until the scene is replaced."""
+        torch = self._torch
+        out = []
+        for which, cols in ((0, 3), (1, 4), (2, 4), (3, None)):
+            ptr, nb = C.c_void_p(), C.c_longlong()
+            _gsr.check(self._lib.gsr_scene_buffer(self._h, which, C.byref(ptr), C.byref(nb)))
+            n_el = nb.value // 4
+
+            class _Raw:  # CUDA array interface over the raw allocation
+                pass
+            raw = _Raw()
+            raw.__cuda_array_interface__ = {"shape": (max(n_el, 0),), "typestr": "<f4", "data": (ptr.value or 0, False),
+                                            "version": 2}
+            t = torch.as_tensor(raw, device=self.device) if n_el > 0 else torch.empty(0, device=self.device)
+            if cols is None:
+                n = out[0].shape[0]
+                cols = (n_el // n) if n else 0
+            out.append(t.view(-1, cols) if n_el else t.view(0, cols or 1))
+        return out
+
     def load_ply(self, path):
         """``load_ply(path)`` + ``update_gaussian_data`` in one step with the decode on the device
         (/root/reference/util_gau.py:63-125 followed by renderer_ogl.py:132-137): the header is parsed
@@ -269,7 +297,12 @@ class B200Renderer(GaussianRenderBase):
             if self._frame is None:
                 self._frame = self._torch.empty((self.h, self.w, 4), dtype=self._torch.float32, device=self.device)
             out = self._frame
-        _gsr.check(self._lib.gsr_render(self._h, C.c_void_p(out.data_ptr()), self._stream()))
+        try:
+            _gsr.check(self._lib.gsr_render(self._h, C.c_void_p(out.data_ptr()), self._stream()))
+        except _gsr.GsrOverflow:
+            # an EARLIER asynchronous frame did not fit the instance buffers (its image was incomplete); the
+            # library has grown them, this frame goes in again
+            _gsr.check(self._lib.gsr_render(self._h, C.c_void_p(out.data_ptr()), self._stream()))
         return out
 
     # ---- read-back (the viewer's glReadPixels) ---------------------------------------------------------
@@ -355,7 +388,10 @@ class B200Renderer(GaussianRenderBase):
         campos = _f32c(campos).reshape(-1, 3)
         n = len(views)
         optr = C.c_void_p(out.data_ptr()) if out is not None else None
-        _gsr.check(self._lib.gsr_render_batch(self._h, _fptr(views), _fptr(campos), n, optr, self._stream()))
+        try:
+            _gsr.check(self._lib.gsr_render_batch(self._h, _fptr(views), _fptr(campos), n, optr, self._stream()))
+        except _gsr.GsrOverflow:  # see draw()
+            _gsr.check(self._lib.gsr_render_batch(self._h, _fptr(views), _fptr(campos), n, optr, self._stream()))
         return out
 
     # ---- introspection --------------------------------------------------------------------------------

@@ -26,6 +26,38 @@ def _psnr(a, b):
     return 99.0 if mse == 0 else 10 * np.log10(1.0 / mse)
 
 
+def _report(line):
+    """Observed parity figures go to stdout (pytest -s) and to gpurun_out/parity_report.txt (merged back from the
+    GPU box; a copy of the last run is committed under profiles/)."""
+    import os
+    print(line)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    try:
+        os.makedirs(os.path.join(root, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(root, "gpurun_out", "parity_report.txt"), "a") as f:
+            f.write(line + "\n")
+    except OSError:
+        pass
+
+
+def _check_image(img, ref, fragile, mod, tag):
+    """The image bar of BASELINE.json: <= 1/255 max-abs per channel and PSNR >= 50 dB against the oracle.  In the
+    hard-threshold modes (-3, -4) pixels the oracle flags as fragile (a 0.22 / 1/255 / power > 0 decision within 2e-5
+    relative of flipping) are exempt; how many were exempt and how many pixels exceed the bar is reported."""
+    diff = np.abs(img - ref).max(axis=-1)
+    frag = fragile.astype(bool) if fragile is not None else np.zeros(diff.shape, bool)
+    over = diff > TOL
+    psnr = _psnr(img[..., :3], ref[..., :3])
+    _report(f"[parity] {tag} mod {mod}: {diff.size} px, max|d| {diff.max():.3e}, over 1/255: {int(over.sum())} "
+            f"(of them fragile {int((over & frag).sum())}), fragile px {int(frag.sum())}, PSNR {psnr:.1f} dB")
+    assert frag.mean() < 5e-3
+    if mod in (-3, -4):
+        assert not (over & ~frag).any(), (tag, mod, diff[~frag].max())
+    else:
+        assert not over.any(), (tag, mod, diff.max())
+    assert psnr >= 50.0, (tag, mod, psnr)
+
+
 @pytest.fixture(scope="module")
 def R():
     from gaussiansplattingviewer_b200.renderer_b200 import B200Renderer
@@ -122,15 +154,7 @@ def test_images_within_tolerance(R, mod, sm):
     ref, fragile, _ = O.render(g, ocam, W, H, clamp_unorm=(mod != -1), want_fragile=True)
     assert img.shape == ref.shape == (H, W, 4)
     assert ref[..., 3].max() > 0.9
-    diff = np.abs(img - ref).max(axis=-1)
-    frag = fragile.astype(bool)
-    assert frag.mean() < 5e-3
-    if mod in (-3, -4):
-        assert diff[~frag].max() <= TOL, (mod, diff[~frag].max())
-        assert (diff > TOL).sum() <= frag.sum()
-    else:
-        assert diff.max() <= TOL, (mod, diff.max())
-    assert _psnr(img[..., :3], ref[..., :3]) >= 50.0
+    _check_image(img, ref, fragile, mod, f"40k/800x450 sm {sm}")
 
 
 def test_config1_golden_images(R, golden):
@@ -149,6 +173,8 @@ def test_config1_golden_images(R, golden):
         img = r.draw().cpu().numpy()
         want = z[f"img_mod{mod}"]
         d = np.abs(img - want)
+        _report(f"[parity] config 1 golden (reference shaders) mod {mod}: max|d| {d.max():.3e}, over 1/255: "
+                f"{int((d.max(axis=-1) > TOL).sum())} of {d.shape[0] * d.shape[1]} px")
         if mod in (-3, -4):
             assert (d.max(axis=-1) > TOL).mean() < 1e-5
         else:
@@ -386,6 +412,34 @@ def test_full_size_properties_3m_1080p(R):
     assert np.isfinite(img).all() and img[..., 3].max() <= 1.0 and img[..., :3].min() >= 0.0
     # idempotence: same state, same image, bit for bit
     assert np.array_equal(_bits(r.draw().cpu().numpy()), _bits(img))
+    # and the image itself against the oracle at the real size (the C oracle needs a second or two on the host cores)
+    cam, pose = scenes.default_view(W, H)
+    ocam = O.make_camera(pose["camera_view"], cam.get_project_matrix(), cam.get_htanfovxy_focal(),
+                         pose["camera_position"], 1.0, 3, g.sh_dim)
+    ref, fragile, _ = O.render(g, ocam, W, H, clamp_unorm=True, want_fragile=True)
+    _check_image(img, ref, fragile, 3, "config 3: 3M SH3 1920x1080")
+
+
+def test_full_size_image_config2_1m_1080p(R):
+    """BASELINE config 2: 1M SH3 at 1920x1080, one view, image against the oracle."""
+    g = scenes.synthetic_gaussians(1_000_000, seed=2)
+    W, H = 1920, 1080
+    r, ocam = _setup(R, g, W, H, debug=False)
+    img = r.draw().cpu().numpy()
+    s = r.stats()
+    assert not s.overflow and s.n_visible > 300_000
+    ref, fragile, _ = O.render(g, ocam, W, H, clamp_unorm=True, want_fragile=True)
+    _check_image(img, ref, fragile, 3, "config 2: 1M SH3 1920x1080")
+    # per-Gaussian records at this size too: bit-exact
+    r.debug = True
+    r.draw()
+    vs_gpu = r.debug_fetch(_gsr.GSR_DBG_VSOUT, np.float32, 16)
+    vs, st = O.preprocess(g, ocam, W, H)
+    assert np.array_equal(_bits(vs_gpu[:, :14]), _bits(vs.view(np.float32).reshape(-1, 16)[:, :14]))
+    vals = r.debug_fetch(_gsr.GSR_DBG_INST_VALS, np.uint32)
+    ranges = r.debug_fetch(_gsr.GSR_DBG_RANGES, np.int32, 2)
+    _, ovals, oranges = O.tile_instances(st, W, H, 32)
+    assert np.array_equal(vals, ovals) and np.array_equal(ranges, oranges)
 
 
 @pytest.mark.parametrize("mod", [3, -1, -3])
@@ -412,9 +466,14 @@ def test_full_size_properties_6m_4k(R, mod):
     if mod != -1:
         assert img[..., :3].min() >= 0.0 and img[..., :3].max() <= 1.0
     del keys, vals
-    r2, _ = _setup(R, g, W, H, mod=mod, keys64=True, debug=False)
+    r2, ocam = _setup(R, g, W, H, mod=mod, keys64=True, debug=False)
     img2 = r2.read_pixels_rgba32f()
     assert np.array_equal(_bits(img2), _bits(img))
+    del r2
+    # the image against the oracle at the real size: colour, the 1.2x-scale disparity pass (gau_vert.glsl:151-156,
+    # 182-211; float target, unclamped) and the flat-ball threshold mode
+    ref, fragile, _ = O.render(g, ocam, W, H, clamp_unorm=(mod != -1), want_fragile=True)
+    _check_image(img, ref, fragile, mod, "config 4: 6M SH3 3840x2160")
 
 
 @pytest.mark.parametrize("mod,sm", [(3, 1.0), (0, 2.0), (-1, 1.0), (-2, 1.0), (-3, 1.0), (-4, 1.0)])

@@ -1,0 +1,110 @@
+"""Failure handling of the C ABI on the GPU: instance-buffer overflow on the asynchronous entry
+points, more than 65536 tiles, a frozen order surviving gsr_sort_depth.  `pytest -m gpu`."""
+import numpy as np
+import pytest
+
+from gaussiansplattingviewer_b200 import _gsr, scenes, util
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def R():
+    from gaussiansplattingviewer_b200.renderer_b200 import B200Renderer
+    return B200Renderer
+
+
+def _renderer(R, g, W, H, mod=3):
+    cam, pose = scenes.default_view(W, H)
+    r = R(W, H)
+    r.update_gaussian_data(g)
+    r.set_render_mod(mod)
+    r.update_camera_intrin(cam)
+    r.update_camera_pose(cam, True, pose)
+    return r, cam, pose
+
+
+def test_draw_after_an_overflowed_frame_is_complete(R):
+    """gsr_render cannot know that its frame overflows; the next draw() sees the sticky counter, the library
+    grows the buffers and the frame is drawn again - never a silently black image for good."""
+    import torch
+    g = scenes.synthetic_gaussians(50000, seed=41)
+    W, H = 640, 360
+    r, _, _ = _renderer(R, g, W, H)
+    want = r.draw().cpu().numpy().copy()
+    assert want[..., 3].max() > 0.9
+    r.set_capacity(2048)
+    first = r.draw().cpu().numpy()          # overflows: incomplete by construction
+    torch.cuda.synchronize()
+    assert r.stats().overflow == 1 and not first.any()
+    second = r.draw().cpu().numpy()         # repaired inside draw()
+    assert np.array_equal(_bits(second), _bits(want))
+    s = r.stats()
+    assert s.overflow == 0 and s.capacity >= s.n_instances
+    # the raw ABI call reports it instead of repairing silently
+    r.set_capacity(2048)
+    r.draw()
+    torch.cuda.synchronize()
+    import ctypes as C
+    rc = r._lib.gsr_render(r._h, C.c_void_p(r._frame.data_ptr()), r._stream())
+    assert rc == _gsr.GSR_EOVERFLOW
+    assert np.array_equal(_bits(r.draw().cpu().numpy()), _bits(want))
+
+
+def test_synchronous_overflow_does_not_poison_the_pipelined_path(R):
+    g = scenes.synthetic_gaussians(40000, seed=42)
+    W, H = 480, 270
+    r, _, _ = _renderer(R, g, W, H)
+    want = r.read_pixels_rgb8().copy()
+    r.set_capacity(1024)
+    got = r.read_pixels_rgb8().copy()       # overflows, grows, re-renders inside the call
+    assert np.array_equal(got, want)
+    bufs = [r.read_pixels_rgb8_async() for _ in range(3)]   # the third call is the first sync point
+    r.sync_host()                                           # must not raise a stale GSR_EOVERFLOW
+    for b in bufs:
+        assert np.array_equal(b, want)
+    cap = r.stats().capacity
+    r.read_pixels_rgb8_async(); r.sync_host()
+    assert r.stats().capacity == cap        # and nothing was grown needlessly
+
+
+def test_more_than_65536_tiles(R):
+    """17 tile bits (4096 x 4352 with 16-px tiles): k_tile_scan keeps out of the sort histograms, the tile sort
+    counts its digits itself; image identical to the 32-px tiling (16 bits, histogram from the scan)."""
+    g = scenes.synthetic_gaussians(60000, seed=43)
+    W, H = 4096, 4352
+    r, _, _ = _renderer(R, g, W, H)
+    r.tune(_gsr.GSR_TUNE_TILE, 32)
+    a = r.draw().cpu().numpy().copy()
+    assert a[..., 3].max() > 0.5
+    r.tune(_gsr.GSR_TUNE_TILE, 16)
+    b = r.draw().cpu().numpy()
+    s = r.stats()
+    assert s.tiles_x * s.tiles_y == 256 * 272 > 65536 and not s.overflow
+    assert np.array_equal(_bits(a), _bits(b))
+    b2 = r.draw().cpu().numpy()             # the forked (untimed) path twice: no stale histogram
+    assert np.array_equal(_bits(a), _bits(b2))
+
+
+def test_gaussian_order_keeps_a_frozen_order(R):
+    g = scenes.synthetic_gaussians(30000, seed=44)
+    W, H = 480, 270
+    r, cam, pose = _renderer(R, g, W, H)
+    r.set_auto_sort(False)
+    r.sort_and_update(cam, True, pose)                     # freezes the order of `pose`
+    _, pose2 = scenes.default_view(W, H, eye=(6.0, 1.0, -8.0))
+    r.update_camera_pose(cam, True, pose2)
+    frozen = r.draw().cpu().numpy().copy()
+    order = r.gaussian_order(pose["camera_view"])          # borrows the sort buffers
+    want, _ = O.sort_depth(g.xyz, pose["camera_view"])
+    assert np.array_equal(order, want)
+    again = r.draw().cpu().numpy()
+    assert np.array_equal(_bits(again), _bits(frozen))     # still the frozen order, not a per-frame sort
+    r.set_auto_sort(True)
+    live = r.draw().cpu().numpy()
+    assert not np.array_equal(_bits(live), _bits(frozen))
