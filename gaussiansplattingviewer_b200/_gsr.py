@@ -13,6 +13,8 @@ GSR_FLAG_KEYS64 = 2
 GSR_FLAG_DEBUG = 4
 GSR_FLAG_OFFICIAL = 8
 
+GSR_SORT_STATIC_MAX_PAIRS = 1 << 22
+
 GSR_DBG_VSOUT = 0
 GSR_DBG_SETUP = 1
 GSR_DBG_INST_KEYS = 2
@@ -77,6 +79,7 @@ SIGNATURES = {
     "gsr_freeze_order": (C.c_int, [_vp, _fp, _vp]),
     "gsr_thaw_order": (C.c_int, [_vp]),
     "gsr_sort_pairs": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int, _vp]),
+    "gsr_sort_pairs_static": (C.c_int, [C.c_int, _vp, _vp, _vp, _vp, _ll, C.c_int, C.c_int, _vp]),
     "gsr_get_stats": (C.c_int, [_vp, C.POINTER(Stats)]),
     "gsr_debug_fetch": (C.c_int, [_vp, C.c_int, _vp, _ll, C.POINTER(_ll)]),
     "gsr_scene_buffer": (C.c_int, [_vp, C.c_int, C.POINTER(_vp), C.POINTER(_ll)]),

@@ -994,6 +994,24 @@ int gsr_sort_pairs(gsr_t* h, int key_bits, void* keys, void* keys_tmp, uint32_t*
     return 0;
 }
 
+// Allocation-free variant of gsr_sort_pairs (no counterpart in the reference):
+// the scratch of the radix passes is a static device array inside libgsr.so.
+int gsr_sort_pairs_static(int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, long long n,
+                          int begin_bit, int end_bit, void* stream) {
+    if (key_bits != 32 && key_bits != 64) return fail(GSR_EINVAL, "key_bits must be 32 or 64");
+    if (n < 0) return fail(GSR_EINVAL, "bad n");
+    if (n > GSR_SORT_STATIC_MAX_PAIRS)
+        return fail(GSR_EINVAL, "gsr_sort_pairs_static: n exceeds GSR_SORT_STATIC_MAX_PAIRS (4194304); use gsr_sort_pairs");
+    if (begin_bit < 0 || end_bit > key_bits || begin_bit > end_bit) return fail(GSR_EINVAL, "bad bit range");
+    if (n == 0 || begin_bit == end_bit) return 0;
+    if (!keys || !keys_tmp || !vals || !vals_tmp) return fail(GSR_EINVAL, "null argument");
+    const char* err = "";
+    const int rc = radix_sort_pairs_static(key_bits, keys, keys_tmp, vals, vals_tmp, n, begin_bit, end_bit, (cudaStream_t)stream, &err);
+    if (rc == -1) return fail(GSR_EINVAL, err);
+    if (rc) return fail(GSR_ECUDA, std::string("gsr_sort_pairs_static: ") + err);
+    return 0;
+}
+
 int gsr_get_stats(gsr_t* h, gsr_stats* out) {
     if (!h || !out) return fail(GSR_EINVAL, "null argument");
     CK(cudaSetDevice(h->device));

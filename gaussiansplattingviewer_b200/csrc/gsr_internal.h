@@ -124,6 +124,10 @@ template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
                      long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
                      SortScratch* scratch, cudaStream_t stream, long long* launch_count, const SortOptions* opt = nullptr);
+// the same sort with its scratch in a static device array (no allocation); see radix_sort.cu
+long long radix_sort_static_max_items();
+int radix_sort_pairs_static(int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, long long n,
+                            int begin_bit, int end_bit, cudaStream_t stream, const char** err);
 void launch_tile_scan(int* grid, int grid_stride, int gw, int tiles_x, int tiles_y, int bits0, long long capacity, int2* ranges,
                       uint32_t* hist, FrameCounters* counters, cudaStream_t s);
 

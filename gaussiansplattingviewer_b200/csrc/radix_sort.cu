@@ -656,3 +656,61 @@ template int radix_sort_pairs<uint32_t>(const uint32_t*, uint32_t*, uint32_t*, u
                                         long long, int, int, SortScratch*, cudaStream_t, long long*, const SortOptions*);
 template int radix_sort_pairs<uint64_t>(const uint64_t*, uint64_t*, uint64_t*, uint32_t*, uint32_t*, bool, long long, const uint32_t*,
                                         long long, int, int, SortScratch*, cudaStream_t, long long*, const SortOptions*);
+
+// ---- allocation-free sort (gsr_sort_pairs_static) ---------------------------------------------------------------
+// The radix passes need scratch (digit histograms, tile tickets, two buffers of look-back rows).  Callers that must
+// not call cudaMalloc get the same sort with that scratch in a static device array of fixed size: every GPU that
+// loads libgsr.so holds RS_STATIC_WORDS * 4 bytes (about 5.6 MB) until the process exits.  All calls on a device share
+// the array; the sort clears what must start at zero (histograms + tickets by memset, the first look-back rows by the
+// histogram kernel, the next pass's rows by each pass), so stale contents of an earlier call are harmless - but two
+// calls that OVERLAP on one GPU (different streams) race on it.
+constexpr long long RS_STATIC_MAX_ITEMS = 1ll << 22;  // pairs per call
+constexpr size_t RS_STATIC_TILES = (size_t)(RS_STATIC_MAX_ITEMS / (RS_THREADS * 6) + 2);  // 64-bit keys: smallest tiles
+constexpr size_t RS_STATIC_WORDS = (8 * 256 + 64) + 2 * RS_STATIC_TILES * 256;
+static __device__ __align__(256) uint32_t g_rs_static_scratch[RS_STATIC_WORDS];
+
+long long radix_sort_static_max_items() { return RS_STATIC_MAX_ITEMS; }
+
+// Device address of the static scratch on the CURRENT device.  g_rs_static_scratch is, in host code, only a stand-in
+// for the symbol: the address a kernel can use comes from cudaGetSymbolAddress, once per device with that device current.
+static uint32_t* rs_static_scratch_ptr(const char** err) {
+    static uint32_t* ptr[64] = {};
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { *err = "no current CUDA device"; return nullptr; }
+    if (!ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_rs_static_scratch);
+        if (e != cudaSuccess || !p) { *err = cudaGetErrorString(e); cudaGetLastError(); return nullptr; }
+        ptr[dev] = static_cast<uint32_t*>(p);
+    }
+    return ptr[dev];
+}
+
+// 0 ok (result in keys / vals), -1 bad argument, -2 CUDA error; *err gets a static message.  Allocates nothing.
+int radix_sort_pairs_static(int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, long long n,
+                            int begin_bit, int end_bit, cudaStream_t stream, const char** err) {
+    *err = "";
+    if (n > RS_STATIC_MAX_ITEMS) { *err = "n exceeds the static scratch (GSR_SORT_STATIC_MAX_PAIRS = 4194304 pairs)"; return -1; }
+    uint32_t* base = rs_static_scratch_ptr(err);
+    if (!base) return -2;
+    const int kb = key_bits / 8;
+    SortScratch ss;
+    sort_scratch_carve(&ss, base, RS_STATIC_MAX_ITEMS, kb);
+    if ((size_t)((ss.status[1] + (size_t)ss.max_tiles * 256) - base) > RS_STATIC_WORDS) { *err = "static scratch too small (internal)"; return -2; }
+    int r;
+    if (kb == 4)
+        r = radix_sort_pairs<uint32_t>((uint32_t*)keys, (uint32_t*)keys, (uint32_t*)keys_tmp, vals, vals_tmp, false, n, nullptr, n,
+                                       begin_bit, end_bit, &ss, stream, nullptr);
+    else
+        r = radix_sort_pairs<uint64_t>((uint64_t*)keys, (uint64_t*)keys, (uint64_t*)keys_tmp, vals, vals_tmp, false, n, nullptr, n,
+                                       begin_bit, end_bit, &ss, stream, nullptr);
+    if (r == 1) {  // odd number of passes: bring the result back to keys / vals
+        if (cudaMemcpyAsync(keys, keys_tmp, (size_t)n * kb, cudaMemcpyDeviceToDevice, stream) != cudaSuccess ||
+            cudaMemcpyAsync(vals, vals_tmp, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream) != cudaSuccess) {
+            *err = "copy back failed"; cudaGetLastError(); return -2;
+        }
+    }
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { *err = cudaGetErrorString(e); return -2; }
+    return 0;
+}

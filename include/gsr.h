@@ -192,6 +192,19 @@ int gsr_thaw_order(gsr_t* h);
 int gsr_sort_pairs(gsr_t* h, int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp,
                    long long n, int begin_bit, int end_bit, void* stream);
 
+/* gsr_sort_pairs without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments and result as gsr_sort_pairs minus the handle (it works on the CURRENT device; vals must not be
+ * NULL); the scratch of the radix passes (digit histograms, tile tickets, look-back rows) is a static device array
+ * inside libgsr.so, about 5.6 MB held by every GPU that loads the library until the process exits.
+ * Limit: n <= GSR_SORT_STATIC_MAX_PAIRS, larger calls return GSR_EINVAL with a message.  The call makes no cudaMalloc /
+ * cudaFree (nor any allocating library call).  Every call on a device shares the one array, which keeps the last call's
+ * contents; the sort itself clears what must start at zero, but two calls that OVERLAP on the same GPU (different
+ * streams, or threads) race on it - serialise them.  Asynchronous on `stream`. */
+#define GSR_SORT_STATIC_MAX_PAIRS (1ll << 22)
+int gsr_sort_pairs_static(int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, long long n,
+                          int begin_bit, int end_bit, void* stream);
+
 /* ---- introspection ----------------------------------------------------------------------------- */
 int gsr_get_stats(gsr_t* h, gsr_stats* out); /* synchronises */
 int gsr_debug_fetch(gsr_t* h, int which, void* dst_host, long long capacity_bytes, long long* out_bytes);
