@@ -119,13 +119,14 @@ def stage_bytes(n, v, d, tiles, w, h, sh_dim, keys64):
         passes = -(-(32 + tbits) // 8)
         return {"preprocess": k1, "sort_depth": 0, "ranges": 8 * tiles, "duplicate": 8 * n + 4 * v + 12 * d,
                 "sort_tiles": (8 + 24 * passes) * d + 8 * d, "blend": 52 * d + 16 * w * h}
-    # depth sort over N: first pass (4 in, 8 out) + three passes (8 in, 8 out); its digit histograms are kept by
-    # the preprocess kernel, there is no histogram read
-    # duplicate: sorted index (4) + tile rect (8) per Gaussian in, (tile, index) per instance out
+    # depth sort: the compacting first pass reads the N keys (4 B) and writes (key', index) for the V Gaussians that
+    # have one (8 B); pass two moves V pairs (8 in, 8 out); pass three reads V pairs and writes only the indices
+    # (8 in, 4 out).  Its digit histograms are kept by the preprocess kernel, there is no histogram read.
+    # duplicate: sorted index (4) + tile rect (8) per VISIBLE Gaussian in, (tile, index) per instance out
     # tile sort: the histograms come from k_tile_scan; pass 1 moves pairs (8 in, 8 out), pass 2 reads pairs and
     # writes only the indices (8 in, 4 out); a third pass exists above 65536 tiles
     tile_passes = 1 if tbits <= 8 else (2 if tbits <= 16 else 3)
-    return {"preprocess": k1, "sort_depth": (12 + 16 * 3) * n, "ranges": 8 * tiles, "duplicate": 12 * n + 8 * d,
+    return {"preprocess": k1, "sort_depth": 4 * n + 28 * v, "ranges": 8 * tiles, "duplicate": 12 * v + 8 * d,
             "sort_tiles": (16 * tile_passes - 4) * d, "blend": 52 * d + 16 * w * h}
 
 

@@ -21,15 +21,8 @@ GSR_DBG_INST_KEYS = 2
 GSR_DBG_INST_VALS = 3
 GSR_DBG_RANGES = 4
 
-GSR_TUNE_BLEND_PPT = 0
-GSR_TUNE_SORT_SMALL_TILES = 1
-GSR_TUNE_BLEND_SHAPE8 = 2
-GSR_TUNE_BLEND_SKIP = 3
-GSR_TUNE_SORT_PREFETCH = 4
-GSR_TUNE_SORT_MATCH_MIX = 5
 GSR_TUNE_FRAME_FORK = 6
 GSR_TUNE_TILE = 7
-GSR_TUNE_SORT_BALANCE = 8
 GSR_TUNE_FUSED_DEPTH_HIST = 9
 GSR_TUNE_PDL = 10
 GSR_TUNE_FUSED_RGB8 = 11

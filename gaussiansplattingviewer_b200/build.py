@@ -36,7 +36,8 @@ def _stale(target: str, deps) -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    hdrs = [os.path.join(CSRC, "gsr_internal.h"), os.path.join(HERE, "..", "include", "gsr.h"), os.path.abspath(__file__)]
+    hdrs = [os.path.join(CSRC, "gsr_internal.h"), os.path.join(HERE, "..", "include", "gsr.h"),
+            os.path.join(HERE, "..", "include", "gsr_measure.h"), os.path.abspath(__file__)]
     objs = []
     for src, extra in SOURCES.items():
         s = os.path.join(CSRC, src)

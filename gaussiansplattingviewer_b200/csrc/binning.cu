@@ -63,6 +63,8 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
     __shared__ unsigned long long s_prefix;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t tiles_x = (uint32_t)fp->tiles_x;
+    // the two-level path walks a depth order of counters->n_keys entries (all N, or only the Gaussians with a key)
+    if (!KEYS64) n = min(n, counters->n_keys);
     const unsigned n_chunks = (n + DUP_CHUNK - 1) / DUP_CHUNK;
 
     auto emit = [&](unsigned long long dst, uint32_t tile, uint32_t g) {
@@ -419,16 +421,7 @@ __global__ void k_keys64_from_ranges(const int2* __restrict__ ranges, int n_tile
     }
 }
 
-int sm_count() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
-    }
-    return n;
-}
+int sm_count() { return sm_count_current(); }
 
 }  // namespace
 
@@ -483,10 +476,12 @@ static size_t tile_scan_smem(int gw, int TY) {
 void launch_tile_scan(int* grid, int grid_stride, int gw, int tiles_x, int tiles_y, int bits0, long long capacity, int2* ranges,
                       uint32_t* hist, FrameCounters* counters, cudaStream_t s) {
     const size_t smem = tile_scan_smem(gw, tiles_y);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
+    static bool configured[64] = {};  // per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > 48 * 1024 && dev >= 0 && dev < 64 && !configured[dev]) {
         cudaFuncSetAttribute(k_tile_scan, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(200 * 1024));
-        configured = 200 * 1024;
+        configured[dev] = true;
     }
     k_tile_scan<<<1, TS_THREADS, smem, s>>>(grid, grid_stride, gw, tiles_x, tiles_y, bits0, smem ? 1 : 0,
                                              (unsigned long long)capacity, ranges, hist, counters);

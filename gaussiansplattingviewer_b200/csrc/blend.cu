@@ -502,14 +502,7 @@ __global__ void k_pack_disp_u16(const float4* __restrict__ rgba, uint16_t* __res
     d[i] = (uint16_t)(unsigned)q;
 }
 
-// kernel-variant knobs (gsr_tune): pixels per thread, warp block shape, warp-level quad skip
-int g_blend_ppt = 0, g_blend_shape8 = 1, g_blend_skip = 3;  // ppt 0 = automatic: 2 on 16x16 tiles, 4 on 32x32
-
 }  // namespace
-
-void set_blend_ppt(int v) { if (v == 0 || v == 1 || v == 2 || v == 4) g_blend_ppt = v; }
-void set_blend_shape8(int v) { g_blend_shape8 = v ? 1 : 0; }
-void set_blend_skip(int v) { g_blend_skip = (v >= 0 && v <= 3) ? v : 1; }
 
 // default configuration (every mode, and the counting variant)
 constexpr int BL_PPT = 2;
@@ -533,7 +526,6 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
         if (render_mod == -2) launch_pdl_m(4, k_blend<2, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
         else if (render_mod == -3) launch_pdl_m(4, k_blend<3, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
         else if (render_mod == -4) launch_pdl_m(4, k_blend<4, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
-        else if (!COUNT && g_blend_ppt == 2) launch_pdl_m(4, k_blend<0, 2, false, true, BL_SKIP, 32>, dim3(grid), dim3(512), 0, s, BL_ARGS);
         else launch_pdl_m(4, k_blend<0, P32, COUNT, true, SK32, 32>, dim3(grid), dim3(TH32), 0, s, BL_ARGS);
         return;
     }
@@ -544,20 +536,9 @@ static void launch_blend_t(const FrameParams* fp, const int2* ranges, const uint
     else if (render_mod == -2) launch_pdl_m(4, k_blend<2, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
     else if (render_mod == -3) launch_pdl_m(4, k_blend<3, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
     else if (render_mod == -4) launch_pdl_m(4, k_blend<4, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
-    else if (COUNT) launch_pdl_m(4, k_blend<0, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
-    else {
-        // measurement variants of the main mode
-        const int sk = g_blend_skip;
-        if (g_blend_ppt == 4) {
-            if (g_blend_shape8) { if (sk == 2) launch_pdl_m(4, k_blend<0, 4, false, true, 2>, dim3(grid), dim3(64), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 4, false, true, 1>, dim3(grid), dim3(64), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 4, false, true, 0>, dim3(grid), dim3(64), 0, s, BL_ARGS); }
-            else { if (sk) launch_pdl_m(4, k_blend<0, 4, false, false, 1>, dim3(grid), dim3(64), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 4, false, false, 0>, dim3(grid), dim3(64), 0, s, BL_ARGS); }
-        } else if (g_blend_ppt == 1) {
-            if (sk == 2) launch_pdl_m(4, k_blend<0, 1, false, true, 2>, dim3(grid), dim3(256), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 1, false, true, 1>, dim3(grid), dim3(256), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 1, false, true, 0>, dim3(grid), dim3(256), 0, s, BL_ARGS);
-        } else {
-            if (g_blend_shape8) { if (sk == 3) launch_pdl_m(4, k_blend<0, 2, false, true, 3>, dim3(grid), dim3(128), 0, s, BL_ARGS); else if (sk == 2) launch_pdl_m(4, k_blend<0, 2, false, true, 2>, dim3(grid), dim3(128), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 2, false, true, 1>, dim3(grid), dim3(128), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 2, false, true, 0>, dim3(grid), dim3(128), 0, s, BL_ARGS); }
-            else { if (sk == 2) launch_pdl_m(4, k_blend<0, 2, false, false, 2>, dim3(grid), dim3(128), 0, s, BL_ARGS); else if (sk) launch_pdl_m(4, k_blend<0, 2, false, false, 1>, dim3(grid), dim3(128), 0, s, BL_ARGS); else launch_pdl_m(4, k_blend<0, 2, false, false, 0>, dim3(grid), dim3(128), 0, s, BL_ARGS); }
-        }
-    }
+    else launch_pdl_m(4, k_blend<0, BL_PPT, COUNT, BL_SHAPE8, SK>, dim3(grid), dim3(TH), 0, s, BL_ARGS);
+    // (the pixels-per-thread / block-shape / skip-level variants measured in round 1 are gone: DESIGN.md section 5 keeps
+    // their numbers)
 #undef BL_ARGS
 }
 

@@ -12,6 +12,7 @@
 #include <string>
 
 #include "../../include/gsr.h"
+#include "../../include/gsr_measure.h"
 #include "gsr_internal.h"
 
 namespace {
@@ -80,6 +81,7 @@ struct gsr_renderer {
     uint8_t* d_cap[2] = {nullptr, nullptr};  // stereo capture slots: left RGB8 | right RGB8 | disparity u16
     int order_buf = -1;                      // d_gid[] buffer holding a shared depth order (stereo capture, frozen order)
     bool order_frozen = false;               // gsr_freeze_order: frames draw in the stored order
+    bool order_count_dev = false;            // the stored order is compacted: its length lives in d_counters->n_keys
     float frozen_view[16] = {};              // the view of that order (gsr_sort_depth borrows its buffers and re-freezes)
     cudaStream_t copy_stream = nullptr;
     // frame-internal fork: scratch clears and the single-CTA k_tile_scan run beside preprocess / the depth sort
@@ -102,19 +104,17 @@ struct gsr_renderer {
     gsr_stats stats = {};
     cudaEvent_t ev[8] = {};
     long long launches = 0;
+    GsrTune tune;  // gsr_tune state (per handle)
     // scratch for gsr_sort_pairs
     void* d_sortp = nullptr;
     long long sortp_items = 0;
     int sortp_keybytes = 0;
 };
 
-int g_pdl = 11;  // gsr_tune(GSR_TUNE_PDL): bit 0 radix passes, 1 duplicate, 2 blend (measured slower: off), 3 preprocess; 0 = plain launches
+thread_local int g_pdl = 11;  // PDL mask of the handle whose frame this thread is enqueuing (GsrTune.pdl)
 
 namespace {
 
-int g_fused_depth_hist = 1;  // gsr_tune(GSR_TUNE_FUSED_DEPTH_HIST): 0 = the depth sort runs its own histogram kernel
-int g_fused_rgb8 = 1;  // gsr_tune(GSR_TUNE_FUSED_RGB8): 0 = gsr_render_rgb8_host_async converts with k_pack_rgb8
-int g_frame_fork = 1;  // gsr_tune(GSR_TUNE_FRAME_FORK): 0 = every frame runs on one stream
 
 int free_gaussian_buffers(gsr_t* h) {
     dfree(h->d_xyz); dfree(h->d_rot); dfree(h->d_scale_op); dfree(h->d_sh);
@@ -213,6 +213,7 @@ int tile_bits(int n_tiles) {
 int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode = 0,
                  uint8_t* out_rgb8 = nullptr) {
     FrameParams fp = fp_in;
+    g_pdl = h->tune.pdl;
     if (fp.flags & GSR_FLAG_KEYS64) {
         if (h->order_frozen) return fail(GSR_EINVAL, "a frozen order needs the two-level sort (clear GSR_FLAG_KEYS64)");
         order_mode = 0;
@@ -274,7 +275,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     // Untimed frames fork: the scratch clears run beside the preprocess kernel and the single-CTA k_tile_scan
     // beside the depth sort, on the handle's auxiliary stream (joined by events; no host synchronisation).
     // Timed frames stay on one stream so that the per-stage events bracket exactly one stage each.
-    const bool fork = !timed && !keys64 && g_frame_fork;
+    const bool fork = !timed && !keys64 && h->tune.frame_fork;
     cudaStream_t sa = fork ? h->aux_stream : s;
     const long long sort_upper = cap;
     if (timed) cudaEventRecord(h->ev[0], s);
@@ -282,12 +283,23 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
         CK(cudaEventRecord(h->ev_start, s));
         CK(cudaStreamWaitEvent(sa, h->ev_start, 0));
     }
-    // the shader-path preprocess kernel also counts the digits of the depth keys it writes (k_rs_hist is not run)
-    const bool fused_hist = g_fused_depth_hist && !keys64 && !official && order_mode != 2;
+    // Fast depth sort of the shader path: a visible depth lies in [0.1, 100] (depth clip), so its bits minus those of
+    // 0.05 are a 27-bit integer - three 9-bit radix passes.  The preprocess kernel counts those digits while it writes
+    // the keys (no histogram kernel), the first pass drops the culled Gaussians (compaction, ties keep ascending
+    // index), so passes two and three and the duplicate kernel only see the Gaussians that have a key.
+    const bool fused_hist = h->tune.fast_depth_sort && !keys64 && !official && order_mode != 2;
+    fp.depth_k0 = 0x3D4CCCCDu;                        // bits(0.05f)
+    fp.depth_khi = fp.depth_k0 + ((1u << 27) - 1u);   // bits of ~3277: keys outside are clamped (and counted)
+    fp.depth_npass = 3;
+    fp.depth_bits[0] = fp.depth_bits[1] = fp.depth_bits[2] = 9; fp.depth_bits[3] = 0;
     sp.depth_hist = fused_hist ? h->ss_n.hist : nullptr;
+    // entries of the depth order this frame duplicates from: counted by the preprocess kernel (fast path), all N
+    // (generic path), or what the stored order has (reuse)
+    long long n_keys_init = fused_hist ? 0 : N;
+    if (order_mode == 2) n_keys_init = h->order_count_dev ? -1 : N;
     // uniforms, counters, and the clears of the corner-impulse grid and of those histograms in one launch
     launch_set_params(h->d_fp, fp, h->d_counters, s, h->d_tile_grid, (long long)sp.grid_stride * GSR_GRID_REPLICAS,
-                      sp.depth_hist, 4 * 256);
+                      sp.depth_hist, 3 * 512, n_keys_init);
     if (official) launch_preprocess_official(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     else launch_preprocess(h->d_fp, scene, sp, h->d_counters, N, h->sh_dim, s);
     h->launches += 2;
@@ -300,11 +312,32 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     if (!keys64) {
         // depth sort of the N Gaussians (culled ones carry key 0xFFFFFFFF and sort to the end)
         // (the two mantissa bytes of a depth key are spread over their bins, the exponent bytes are not)
-        SortOptions so_n = {0, fused_hist, false, 0x3u, fork};
-        SortOptions so = {scan_hist ? bits0 : 0, scan_hist, true, 0u, fork};
+        SortOptions so_n = {};
+        so_n.vals_only_last = true;   // only the order (the Gaussian indices) is used downstream
+        so_n.scratch_cleared = fork;
+        if (fused_hist) {
+            so_n.n_pass = 3;
+            so_n.pass_bits[0] = so_n.pass_bits[1] = so_n.pass_bits[2] = 9;
+            so_n.hist_ready = true;
+            so_n.hist_stride = 512;
+            so_n.drop_rebase = true;
+            so_n.k0 = fp.depth_k0; so_n.khi = fp.depth_khi;
+            so_n.n_dev_rest = &h->d_counters->n_keys;
+        } else {
+            so_n.hist_direct_mask = 0x3u;  // the two mantissa bytes of a depth key are spread over their bins
+        }
+        SortOptions so = {};
+        so.vals_only_last = true;
+        so.scratch_cleared = fork;
+        if (scan_hist) {  // both digit histograms of the tile sort come from k_tile_scan
+            so.hist_ready = true;
+            so.n_pass = (tbits > bits0) ? 2 : 1;
+            so.pass_bits[0] = bits0;
+            so.pass_bits[1] = tbits - bits0;
+        }
         if (fork) {
-            if (order_mode != 2) sort_scratch_clear<uint32_t>(&h->ss_n, N, fused_hist, sa);
-            sort_scratch_clear<uint32_t>(&h->ss_i, sort_upper, scan_hist, sa);
+            if (order_mode != 2) sort_scratch_clear<uint32_t>(&h->ss_n, N, fused_hist, sa, &so_n);
+            sort_scratch_clear<uint32_t>(&h->ss_i, sort_upper, scan_hist, sa, &so);
             CK(cudaEventRecord(h->ev_cleared, sa));
             CK(cudaEventRecord(h->ev_pre, s));
             CK(cudaStreamWaitEvent(sa, h->ev_pre, 0));
@@ -322,6 +355,7 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
             r0 = radix_sort_pairs<uint32_t>(h->sp.depth_key, h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1],
                                             true, N, nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
             h->order_buf = (order_mode == 1) ? r0 : -1;
+            h->order_count_dev = fused_hist;
         }
         const uint32_t* sorted_gid = h->d_gid[r0];
         if (timed) cudaEventRecord(h->ev[2], s);
@@ -448,6 +482,8 @@ int gsr_create(int device, gsr_t** out) {
         return fail(GSR_ECUDA, std::string("no CUDA device: ") + cudaGetErrorString(e));
     if (device < 0 || device >= count) return fail(GSR_EINVAL, "bad device index");
     CK(cudaSetDevice(device));
+    if (radix_sort_prepare_device() || preprocess_prepare_device())
+        return fail(GSR_ECUDA, "kernel set-up failed on this device (shared-memory opt-in)");
     gsr_t* h = new gsr_renderer();
     h->device = device;
     CK(cudaMalloc(&h->d_fp, sizeof(FrameParams) * 2));
@@ -788,9 +824,9 @@ int gsr_render_rgb8_host_async(gsr_t* h, uint8_t* out, void* stream) {
     if (rc) return rc;
     const long long npx = (long long)h->W * h->H;
     uint8_t* dev = slot ? h->d_rgb8b : h->d_rgb8;
-    rc = render_frame(h, h->fp, h->d_frame, s, false, 0, g_fused_rgb8 ? dev : nullptr);  // the blend kernel packs RGB8 itself
+    rc = render_frame(h, h->fp, h->d_frame, s, false, 0, h->tune.fused_rgb8 ? dev : nullptr);  // the blend kernel packs RGB8 itself
     if (rc) return rc;
-    if (!g_fused_rgb8) {
+    if (!h->tune.fused_rgb8) {
         launch_pack_rgb8(h->d_frame, dev, npx, s);
         h->launches += 1;
     }
@@ -828,10 +864,10 @@ int gsr_capture_stereo_async(gsr_t* h, const float view_left[16], const float ca
     memcpy(fp.campos, campos_left, 12);
     if (left_rgb) {
         fp.flags |= GSR_FLAG_CLAMP_UNORM;  // RGB8 FBO (main.py:846-852)
-        rc = render_frame(h, fp, h->d_frame, s, false, mode, g_fused_rgb8 ? d_left : nullptr);
+        rc = render_frame(h, fp, h->d_frame, s, false, mode, h->tune.fused_rgb8 ? d_left : nullptr);
         if (rc) return rc;
         if (mode) mode = 2;
-        if (!g_fused_rgb8) { launch_pack_rgb8(h->d_frame, d_left, (long long)npx, s); h->launches += 1; }
+        if (!h->tune.fused_rgb8) { launch_pack_rgb8(h->d_frame, d_left, (long long)npx, s); h->launches += 1; }
     }
     if (disparity) {
         FrameParams fd = fp;
@@ -851,9 +887,9 @@ int gsr_capture_stereo_async(gsr_t* h, const float view_left[16], const float ca
         if (mode == 2) {  // the shared order needs equal depth rows; otherwise sort again
             for (int k = 8; k < 12; ++k) if (fr.view[k] != fp.view[k]) mode = 0;
         }
-        rc = render_frame(h, fr, h->d_frame, s, false, mode, g_fused_rgb8 ? d_right : nullptr);
+        rc = render_frame(h, fr, h->d_frame, s, false, mode, h->tune.fused_rgb8 ? d_right : nullptr);
         if (rc) return rc;
-        if (!g_fused_rgb8) { launch_pack_rgb8(h->d_frame, d_right, (long long)npx, s); h->launches += 1; }
+        if (!h->tune.fused_rgb8) { launch_pack_rgb8(h->d_frame, d_right, (long long)npx, s); h->launches += 1; }
     }
     if (!h->order_frozen) h->order_buf = -1;
     CK(cudaEventRecord(h->ev_packed[slot], s));
@@ -904,7 +940,8 @@ int gsr_sort_depth(gsr_t* h, const float view[16], int32_t* out_index, int dst_i
     if (N == 0) return 0;
     launch_depth_keys(h->d_xyz, view, h->d_dkey[0], N, s);
     h->launches += 1;
-    SortOptions so_n = {0, false, false, 0x3u};  // mantissa bytes counted directly, see render_frame
+    SortOptions so_n = {};
+    so_n.hist_direct_mask = 0x3u;  // mantissa bytes counted directly, see render_frame
     const int r = radix_sort_pairs<uint32_t>(h->d_dkey[0], h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1], true, N,
                                              nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
     CK(cudaMemcpyAsync(out_index, h->d_gid[r], (size_t)N * 4,
@@ -932,12 +969,14 @@ int gsr_freeze_order(gsr_t* h, const float view[16], void* stream) {
     const long long N = h->N;
     h->order_buf = 0;
     h->order_frozen = true;
+    h->order_count_dev = false;
     h->frame_valid = false;
     memcpy(h->frozen_view, view, 64);
     if (N == 0) return 0;
     launch_depth_keys(h->d_xyz, view, h->d_dkey[0], N, s, 1);
     h->launches += 1;
-    SortOptions so_n = {0, false, false, 0x3u};
+    SortOptions so_n = {};
+    so_n.hist_direct_mask = 0x3u;
     h->order_buf = radix_sort_pairs<uint32_t>(h->d_dkey[0], h->d_dkey[0], h->d_dkey[1], h->d_gid[0], h->d_gid[1], true, N,
                                               nullptr, N, 0, 32, &h->ss_n, s, &h->launches, &so_n);
     CK(cudaGetLastError());
@@ -1078,22 +1117,16 @@ int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy
 int gsr_tune(gsr_t* h, int key, int value) {
     if (!h) return fail(GSR_EINVAL, "null handle");
     switch (key) {
-        case GSR_TUNE_BLEND_PPT:
-            if (value != 1 && value != 2 && value != 4) return fail(GSR_EINVAL, "blend ppt must be 1, 2 or 4");
-            set_blend_ppt(value);
+        case GSR_TUNE_FUSED_DEPTH_HIST: h->tune.fast_depth_sort = value ? 1 : 0; return 0;
+        case GSR_TUNE_PDL: h->tune.pdl = value; return 0;
+        case GSR_TUNE_FUSED_RGB8: h->tune.fused_rgb8 = value ? 1 : 0; return 0;
+        case GSR_TUNE_FRAME_FORK: h->tune.frame_fork = value ? 1 : 0; return 0;
+        case GSR_TUNE_TILE:
+            if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32");
+            h->tile_req = value;
+            h->frame_valid = false;
             return 0;
-        case GSR_TUNE_BLEND_SHAPE8: set_blend_shape8(value); return 0;
-        case GSR_TUNE_BLEND_SKIP: set_blend_skip(value); return 0;
-        case GSR_TUNE_SORT_PREFETCH: set_sort_prefetch(value); return 0;
-        case GSR_TUNE_SORT_MATCH_MIX: set_sort_mix(value); return 0;
-        case GSR_TUNE_SORT_BALANCE: set_sort_balance(value); return 0;
-        case GSR_TUNE_FUSED_DEPTH_HIST: g_fused_depth_hist = value ? 1 : 0; return 0;
-        case GSR_TUNE_PDL: g_pdl = value; return 0;
-        case GSR_TUNE_FUSED_RGB8: g_fused_rgb8 = value ? 1 : 0; return 0;
-        case GSR_TUNE_FRAME_FORK: g_frame_fork = value ? 1 : 0; return 0;
-        case GSR_TUNE_TILE: if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32"); h->tile_req = value; h->frame_valid = false; return 0;
-        case GSR_TUNE_SORT_SMALL_TILES: set_sort_small_tiles(value); return 0;
-        default: return fail(GSR_EINVAL, "unknown tuning key");
+        default: return fail(GSR_EINVAL, "unknown (or retired) tuning key");
     }
 }
 

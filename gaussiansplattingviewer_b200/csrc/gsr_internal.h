@@ -20,6 +20,11 @@ struct FrameParams {
     int tiles_x, tiles_y;
     unsigned flags;
     int tile_shift;  // log2 of the tile edge in pixels: 4 (16x16) or 5 (32x32, shader path only)
+    // digit plan of the frame's depth sort (the preprocess kernel counts these digits, the compacting first radix
+    // pass applies the same key' = min(max(key, k0), khi) - k0): depth_npass passes of depth_bits[] bits, LSB first
+    unsigned depth_k0, depth_khi;
+    int depth_npass;
+    int depth_bits[4];
 };
 
 // Device-side counters of one frame (zeroed at frame start).
@@ -28,6 +33,8 @@ struct FrameCounters {
     unsigned n_instances;  // D (sum of tiles touched), unclamped
     unsigned overflow;     // D > capacity
     unsigned n_sort;       // instances the tile sort handles: D, or 0 when the buffers overflowed
+    unsigned n_keys;       // entries of the depth order the frame duplicates from (N, or the Gaussians with a depth key)
+    unsigned depth_clamped;  // depth keys outside [depth_k0, depth_khi] (their mutual order is lost; none in a sane frustum)
     // not cleared per frame (pipelined paths read them at a later sync point and clear them there)
     unsigned sticky_overflow;  // frames that overflowed since the last clear
     unsigned sticky_max_d;     // largest D among them
@@ -61,7 +68,7 @@ struct SplatBuffers {
     int grid_stride;      // ints per replica; GSR_GRID_REPLICAS replicas spread the atomics of hot tiles
     float* dbg_vsout;     // N x 16 or nullptr
     int32_t* dbg_setup;   // N x 8 or nullptr
-    uint32_t* depth_hist; // [4][256] digit counts of the depth keys, accumulated by k_preprocess (nullptr: not wanted)
+    uint32_t* depth_hist; // [4][512] digit counts of the rebased depth keys (FrameParams.depth_*), accumulated by k_preprocess (nullptr: not wanted)
 };
 
 // ---- programmatic dependent launch (sm_90+) ---------------------------------------------------------
@@ -69,7 +76,14 @@ struct SplatBuffers {
 // running; it must call pdl_wait() before it touches ANY global memory (the call returns when the kernel in
 // front has completed and its writes are visible; it is a no-op for a plain launch).  What this hides is the
 // launch latency and block scheduling of the next kernel behind the tail of the current one.
-extern int g_pdl;  // gsr_tune(GSR_TUNE_PDL): bit mask, see launch_pdl_m
+// gsr_tune state of a handle; render_frame makes the handle's PDL mask current for the launches it issues
+struct GsrTune {
+    int pdl = 11;              // GSR_TUNE_PDL: bit 0 radix passes, 1 duplicate, 2 blend (measured slower: off), 3 preprocess
+    int fast_depth_sort = 1;   // GSR_TUNE_FUSED_DEPTH_HIST: digit counts from the preprocess kernel + compacting 9-bit passes
+    int fused_rgb8 = 1;        // GSR_TUNE_FUSED_RGB8
+    int frame_fork = 1;        // GSR_TUNE_FRAME_FORK
+};
+extern thread_local int g_pdl;  // PDL mask of the handle whose frame is being enqueued on this thread
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_wait() {
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -100,30 +114,31 @@ size_t sort_scratch_bytes(long long max_items, int key_bytes);
 void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key_bytes);
 
 // Sorts n pairs (n read from *n_dev when n_dev != nullptr, else n_host) on bits [begin_bit, end_bit).
-// keys/vals are ping-ponged with keys_tmp/vals_tmp; the number of passes is made even by the caller or
-// the result location is returned: returns 0 if the result is in keys/vals, 1 if in keys_tmp/vals_tmp.
-// vals_in may be nullptr (identity).  hist_ready: the per-pass histograms were already accumulated into
-// scratch->hist by a producer kernel (skip the histogram kernel and the clear).
-// keys_first: input of the first pass (may equal keys; it is only read), so a key array can be sorted
-// without being overwritten.
-// opt (may be nullptr): first_bits = width of the first digit (0 = 8; later digits are 8 bits wide);
-// hist_ready = scratch->hist already holds the per-pass digit counts (k_tile_scan), skip the histogram
-// kernel; vals_only_last = the last pass does not write keys (the caller only needs the permuted values);
-// hist_direct_mask: see k_rs_hist.
+// keys/vals are ping-ponged with keys_tmp/vals_tmp: returns 0 if the result is in keys/vals, 1 if in
+// keys_tmp/vals_tmp.  vals_identity: the values of the first pass are 0, 1, 2, ... (vals is only written).
+// keys_first: input of the first pass (may equal keys; it is only read), so a key array can be sorted without
+// being overwritten.  opt (may be nullptr, all fields zero = defaults):
 struct SortOptions {
-    int first_bits;
-    bool hist_ready;
-    bool vals_only_last;
-    unsigned hist_direct_mask;  // passes whose digits are spread over their bins: count them without the warp match
-    bool scratch_cleared;       // the caller already ran sort_scratch_clear (e.g. on another stream)
+    int n_pass;                  // > 0: explicit digit plan, pass p sorts pass_bits[p] bits (<= 9) upward from begin_bit
+    int pass_bits[8];
+    bool hist_ready;             // scratch->hist already holds the per-pass digit counts (k_preprocess / k_tile_scan):
+                                 // no histogram kernel
+    int hist_stride;             // words between the passes' histograms in scratch->hist (0 = 256)
+    bool vals_only_last;         // the last pass does not write keys (the caller only needs the permuted values)
+    unsigned hist_direct_mask;   // passes whose digits are spread over their bins: k_rs_hist counts them without the warp match
+    bool scratch_cleared;        // the caller already ran sort_scratch_clear (e.g. on another stream)
+    bool drop_rebase;            // 32-bit keys, identity values: the first pass drops keys == 0xFFFFFFFF and rewrites the
+    uint32_t k0, khi;            // others as min(max(key, k0), khi) - k0; the later passes sort n_dev_rest keys
+    const uint32_t* n_dev_rest;  // device count of the keys that survive the first pass
 };
 // the clears radix_sort_pairs starts with (histograms + tickets, or tickets + first look-back rows when hist_ready)
 template <typename KeyT>
-void sort_scratch_clear(SortScratch* scratch, long long upper, bool hist_ready, cudaStream_t stream);
+void sort_scratch_clear(SortScratch* scratch, long long upper, bool hist_ready, cudaStream_t stream, const SortOptions* opt = nullptr);
 template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
                      long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
                      SortScratch* scratch, cudaStream_t stream, long long* launch_count, const SortOptions* opt = nullptr);
+int radix_sort_prepare_device();  // per-device kernel opt-ins (gsr_create)
 // the same sort with its scratch in a static device array (no allocation); see radix_sort.cu
 long long radix_sort_static_max_items();
 int radix_sort_pairs_static(int key_bits, void* keys, void* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, long long n,
@@ -132,8 +147,10 @@ void launch_tile_scan(int* grid, int grid_stride, int gw, int tiles_x, int tiles
                       uint32_t* hist, FrameCounters* counters, cudaStream_t s);
 
 // ---- kernels' host launchers ---------------------------------------------------------------------
+// n_keys_init: value of counters->n_keys at frame start (-1 = keep: the frame reuses a stored depth order)
 void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s,
-                       int* zero_a = nullptr, long long na = 0, uint32_t* zero_b = nullptr, int nb = 0);
+                       int* zero_a = nullptr, long long na = 0, uint32_t* zero_b = nullptr, int nb = 0,
+                       long long n_keys_init = 0);
 void launch_pack_scene(const float* rot, const float* scale, const float* opacity, float4* rot4, float4* scale_op,
                        long long n, cudaStream_t s);
 void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers out, FrameCounters* counters,
@@ -143,6 +160,7 @@ void launch_preprocess_official(const FrameParams* fp, SceneBuffers scene, Splat
                                 long long n, int sh_dim, cudaStream_t s);
 void launch_depth_keys(const float* xyz, const float* view16_host, uint32_t* keys, long long n, cudaStream_t s, int negate = 0);
 // big_list: N uint4 entries, big_count: one zeroed counter (large rectangles, see binning.cu)
+// n: upper bound of the entries of sorted_gid; the kernel reads counters->n_keys (<= n) entries
 void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, SplatBuffers sp,
                              FrameCounters* counters, uint32_t* chain_status, uint32_t* chain_ticket,
                              uint32_t* out_tile, uint32_t* out_gid, uint4* big_list, uint32_t* big_count, long long n,
@@ -164,13 +182,8 @@ void launch_keys64_from_ranges(const int2* ranges, int n_tiles, const uint32_t* 
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                         float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
                         unsigned long long* pair_counts, cudaStream_t s, int tile = 16);
-void set_blend_ppt(int v);
-void set_blend_shape8(int v);
-void set_blend_skip(int v);
-void set_sort_small_tiles(int v);
-void set_sort_prefetch(int v);
-void set_sort_mix(int v);
-void set_sort_balance(int v);
+int preprocess_prepare_device();  // per-device kernel opt-ins (gsr_create)
+int sm_count_current();           // SM count of the current device (cached per device)
 int measure_peaks_impl(float* fp32_tflops, float* ex2_tops, float* copy_gbs);
 
 // ---- PLY decode (ply_decode.cu) ----------------------------------------------------------------

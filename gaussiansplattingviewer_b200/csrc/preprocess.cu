@@ -90,6 +90,8 @@ struct SharedParams {
     int render_mod, W, H, tiles_x, tiles_y;
     unsigned flags;
     int tile_shift;
+    unsigned depth_k0, depth_khi;
+    int depth_npass, depth_shift[4], depth_mask[4];
 };
 
 template <int SH_DIM, bool DEBUG>
@@ -108,16 +110,24 @@ __global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __rest
     // digit counts of the depth keys this CTA writes (the four passes of the depth sort need them): the CTAs are
     // persistent, so the counts stay in shared memory for the whole kernel and go out once per CTA - the depth
     // sort's histogram kernel (32 us over 3 M keys, bound by shared-memory atomics) is not launched
-    __shared__ uint32_t s_dh[4 * 256];
-    for (int i = threadIdx.x; i < 4 * 256; i += 256) s_dh[i] = 0;
+    __shared__ uint32_t s_dh[3 * 512];  // up to three 9-bit digits of the rebased depth key
+    for (int i = threadIdx.x; i < 3 * 512; i += 256) s_dh[i] = 0;
     pdl_wait();  // resident behind k_set_params: uniforms and cleared scratch are read after this
-    unsigned n_culled = 0;
+    unsigned n_keys = 0, n_clamped = 0;
     if (threadIdx.x < 16) { P.view[threadIdx.x] = fp->view[threadIdx.x]; P.proj[threadIdx.x] = fp->proj[threadIdx.x]; }
     if (threadIdx.x == 32) {
         P.htanx = fp->htanx; P.htany = fp->htany; P.focal = fp->focal;
         P.campos[0] = fp->campos[0]; P.campos[1] = fp->campos[1]; P.campos[2] = fp->campos[2];
         P.scale_modifier = fp->scale_modifier; P.render_mod = fp->render_mod;
         P.W = fp->W; P.H = fp->H; P.tiles_x = fp->tiles_x; P.tiles_y = fp->tiles_y; P.flags = fp->flags; P.tile_shift = fp->tile_shift;
+        P.depth_k0 = fp->depth_k0; P.depth_khi = fp->depth_khi;
+        P.depth_npass = fp->depth_npass < 3 ? fp->depth_npass : 3;
+        int sh = 0;
+        for (int p = 0; p < 4; ++p) {
+            const int b = (p < fp->depth_npass) ? fp->depth_bits[p] : 0;
+            P.depth_shift[p] = sh; P.depth_mask[p] = (1 << b) - 1;
+            sh += b;
+        }
         s_visible = 0;
     }
     __syncthreads();
@@ -394,15 +404,15 @@ __global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __rest
             }
             out.depth_key[g] = dk;
             out.trect[g] = trect;
-            if (out.depth_hist) {
-                if (dk != 0xFFFFFFFFu) {
-                    atomicAdd(&s_dh[dk & 255u], 1u);
-                    atomicAdd(&s_dh[256 + ((dk >> 8) & 255u)], 1u);
-                    atomicAdd(&s_dh[512 + ((dk >> 16) & 255u)], 1u);
-                    atomicAdd(&s_dh[768 + (dk >> 24)], 1u);
-                } else {
-                    ++n_culled;  // key 0xFFFFFFFF: digit 255 of every pass, added once per CTA below
-                }
+            if (out.depth_hist && dk != 0xFFFFFFFFu) {
+                // digits of the key the compacting radix pass will write (culled Gaussians are dropped there)
+                const unsigned kc = min(max(dk, P.depth_k0), P.depth_khi);
+                n_clamped += (kc != dk) ? 1u : 0u;
+                const unsigned kp = kc - P.depth_k0;
+                ++n_keys;
+#pragma unroll
+                for (int p = 0; p < 3; ++p)
+                    if (p < P.depth_npass) atomicAdd(&s_dh[p * 512 + ((kp >> P.depth_shift[p]) & P.depth_mask[p])], 1u);
             }
         }
         if (DEBUG && in) {
@@ -428,13 +438,14 @@ __global__ void __launch_bounds__(256, 3) k_preprocess(const FrameParams* __rest
     __syncthreads();
     if (threadIdx.x == 0 && s_visible) atomicAdd(&counters->n_visible, s_visible);
     if (out.depth_hist) {
-        n_culled = __reduce_add_sync(0xffffffffu, n_culled);
-        if ((threadIdx.x & 31) == 0 && n_culled) {
-            atomicAdd(&s_dh[255], n_culled); atomicAdd(&s_dh[256 + 255], n_culled);
-            atomicAdd(&s_dh[512 + 255], n_culled); atomicAdd(&s_dh[768 + 255], n_culled);
+        n_keys = __reduce_add_sync(0xffffffffu, n_keys);
+        n_clamped = __reduce_add_sync(0xffffffffu, n_clamped);
+        if ((threadIdx.x & 31) == 0) {
+            if (n_keys) atomicAdd(&counters->n_keys, n_keys);
+            if (n_clamped) atomicAdd(&counters->depth_clamped, n_clamped);
         }
         __syncthreads();
-        for (int i = threadIdx.x; i < 4 * 256; i += 256) {
+        for (int i = threadIdx.x; i < P.depth_npass * 512; i += 256) {
             const uint32_t c = s_dh[i];
             if (c) atomicAdd(&out.depth_hist[i], c);
         }
@@ -637,10 +648,15 @@ __global__ void __launch_bounds__(256) k_preprocess_official(const FrameParams* 
 // corner-impulse grid and the depth-digit histograms) - one launch instead of a kernel and two memsets in front
 // of the frame's first real kernel.
 __global__ void __launch_bounds__(256) k_set_params(FrameParams* dst, FrameParams fp, FrameCounters* counters,
-                                                    int* __restrict__ zero_a, long long na, uint32_t* __restrict__ zero_b, int nb) {
+                                                    int* __restrict__ zero_a, long long na, uint32_t* __restrict__ zero_b, int nb,
+                                                    long long n_keys_init) {
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         *dst = fp;
-        if (counters) { counters->n_visible = 0; counters->n_instances = 0; counters->overflow = 0; counters->n_sort = 0; }
+        if (counters) {
+            counters->n_visible = 0; counters->n_instances = 0; counters->overflow = 0; counters->n_sort = 0;
+            counters->depth_clamped = 0;
+            if (n_keys_init >= 0) counters->n_keys = (unsigned)n_keys_init;
+        }
     }
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -680,12 +696,37 @@ __global__ void k_depth_keys(const float* __restrict__ xyz, View16 vm, uint32_t*
 }  // namespace
 
 void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* counters, cudaStream_t s, int* zero_a,
-                       long long na, uint32_t* zero_b, int nb) {
+                       long long na, uint32_t* zero_b, int nb, long long n_keys_init) {
     const long long work = (na > nb ? na : nb);
     long long grid = (work + 255) / 256;
     if (grid < 1) grid = 1;
     if (grid > 296) grid = 296;
-    k_set_params<<<(unsigned)grid, 256, 0, s>>>(dst, fp, counters, zero_a, zero_a ? na : 0, zero_b, zero_b ? nb : 0);
+    k_set_params<<<(unsigned)grid, 256, 0, s>>>(dst, fp, counters, zero_a, zero_a ? na : 0, zero_b, zero_b ? nb : 0, n_keys_init);
+}
+
+int sm_count_current() {
+    static int cache[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (cache[dev] == 0) {
+        cudaDeviceGetAttribute(&cache[dev], cudaDevAttrMultiProcessorCount, dev);
+        if (cache[dev] <= 0) cache[dev] = 148;
+    }
+    return cache[dev];
+}
+
+// persistent CTAs: 3 per SM (8 warps x (32 x 13 + 88) float4 of staging each)
+static constexpr int PRE_SMEM = 8 * (32 * 13 + 88) * (int)sizeof(float4);
+int preprocess_prepare_device() {  // opt-ins for the CURRENT device (gsr_create)
+    bool ok = true;
+    ok = cudaFuncSetAttribute(k_preprocess<48, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM) == cudaSuccess && ok;
+    ok = cudaFuncSetAttribute(k_preprocess<48, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM) == cudaSuccess && ok;
+    ok = cudaFuncSetAttribute(k_preprocess<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM) == cudaSuccess && ok;
+    ok = cudaFuncSetAttribute(k_preprocess<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, PRE_SMEM) == cudaSuccess && ok;
+    ok = cudaFuncSetAttribute(k_preprocess<48, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess && ok;
+    if (!ok) cudaGetLastError();
+    return ok ? 0 : -1;
 }
 
 void launch_pack_scene(const float* rot, const float* scale, const float* opacity, float4* rot4, float4* scale_op,
@@ -698,19 +739,9 @@ void launch_preprocess(const FrameParams* fp, SceneBuffers scene, SplatBuffers o
                        long long n, int sh_dim, cudaStream_t s) {
     if (n <= 0) return;
     const bool dbg = out.dbg_vsout != nullptr;
-    // persistent CTAs: 3 per SM (8 warps x (32 x 13 + 88) float4 of staging each), chunks of 256 Gaussians round-robin
-    const int smem = 8 * (32 * 13 + 88) * (int)sizeof(float4);
-    static int sm_count = 0;
-    if (!sm_count) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-        cudaFuncSetAttribute(k_preprocess<48, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        cudaFuncSetAttribute(k_preprocess<48, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        cudaFuncSetAttribute(k_preprocess<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        cudaFuncSetAttribute(k_preprocess<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        cudaFuncSetAttribute(k_preprocess<48, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-    }
+    // persistent CTAs: 3 per SM, chunks of 256 Gaussians round-robin (opt-ins: preprocess_prepare_device)
+    const int smem = PRE_SMEM;
+    const int sm_count = sm_count_current();
     const long long chunks = (n + 255) / 256;
     const unsigned grid = (unsigned)(chunks < 3LL * sm_count ? chunks : 3LL * sm_count);
     if (sh_dim == 48) {

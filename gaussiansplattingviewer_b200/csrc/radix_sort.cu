@@ -16,6 +16,8 @@
 //
 // Item counts may live on the device (n_dev): grids are sized for the SM count, not for n, so the
 // same launch (and the same captured CUDA graph) serves any n up to the buffer capacity.
+#include <cstdlib>
+
 #include "gsr_internal.h"
 
 namespace {
@@ -32,10 +34,6 @@ constexpr uint32_t RS_VAL_MASK = (1u << 30) - 1u;
 template <typename KeyT> struct RsCfg;
 template <> struct RsCfg<uint32_t> { static constexpr int LARGE = 16, SMALL = 8; };
 template <> struct RsCfg<uint64_t> { static constexpr int LARGE = 12, SMALL = 6; };
-int g_rs_small = 0;
-int g_rs_prefetch = 1;
-int g_rs_balance = 1;  // k_rs_pass2: 1 = equal spans per CTA (gsr_tune GSR_TUNE_SORT_BALANCE)
-int g_rs_mix = 0;  // k_rs_pass2: 1 = odd items are matched by MATCH.ANY (ADU pipe) instead of ballots (measured slower)
 
 struct RsPasses {
     int n;
@@ -113,6 +111,156 @@ __device__ __forceinline__ uint32_t look_back(const uint32_t* status, long long 
     return prefix;
 }
 
+template <int BITS>
+__device__ __forceinline__ uint32_t match_digit_t(uint32_t d) {
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < BITS; ++b) {
+        asm("{\n\t"
+            ".reg .pred p;\n\t"
+            ".reg .b32 t, m;\n\t"
+            "and.b32 t, %1, %2;\n\t"
+            "setp.ne.b32 p, t, 0;\n\t"
+            "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+            "@p and.b32 %0, %0, m;\n\t"
+            "@!p lop3.b32 %0, %0, m, 0, 0x30;\n\t"
+            "}"
+            : "+r"(peers)
+            : "r"(d), "r"(1u << b));
+    }
+    return peers;
+}
+
+// ---- inter-tile prefixes of k_rs_pass3: two-level sums behind per-tile flags --------------------------------------
+// The decoupled look-back of k_rs_pass (every thread walks back over the count rows of its digit until it meets an
+// inclusive prefix) is a poor fit for persistent CTAs that run in lock step: all tiles of a wave finish ranking at about
+// the same time, the front of inclusive prefixes then advances a window per L2 round trip, and all 256 threads of
+// every waiting CTA spin on 16 volatile loads each, taking issue slots from the CTAs that still rank (ncu: half of the
+// executed instructions and 45 % of the stall samples of a pass were that loop; switching it off - wrong result, timing
+// only - took 13 to 18 us off a 45 us pass).  Here nothing is chained:
+//   * a tile publishes its count row (AGG) and then ONE flag word;
+//   * tiles form groups of RS_GROUP; the tile that completes a group (atomic arrival counter) sums the group's rows
+//     into a GROUP row behind a group flag;
+//   * the first tile of a group publishes the exclusive prefix at the start of the group (a checkpoint) once it has it;
+//   * a tile's prefix = nearest checkpoint + GROUP rows since + the rows of the tiles in front of it in its own group:
+//     at most (tiles in flight) / RS_GROUP + RS_GROUP rows, all loads independent.
+// Waiting is done by warp 0 alone (one coalesced load of flag words per poll, with a back-off) while the other warps sit
+// at the barrier.  Every wait is for a tile with a smaller ticket, so forward progress needs what the look-back needed.
+// One status buffer: [flag words: tile_flag[R] | group_cnt[G] | group_flag[G] | ckpt_flag[G]] [AGG R rows] [GROUP G rows]
+// [CKPT G rows], R = rows, G = R / RS_GROUP + 1, rows of `stride` words.  Only the flag words have to start at zero.
+constexpr int RS_GROUP = 16;
+struct RsStatus {
+    uint32_t* tile_flag; uint32_t* group_cnt; uint32_t* group_flag; uint32_t* ckpt_flag;
+    uint32_t* agg; uint32_t* group; uint32_t* ckpt;
+    long long flag_words;
+};
+__host__ __device__ constexpr long long rs_status_groups(long long rows) { return rows / RS_GROUP + 1; }
+__host__ __device__ constexpr long long rs_status_flag_words(long long rows) { return (rows + 3 * rs_status_groups(rows) + 511) & ~511ll; }
+// words of one status buffer with rows of up to 512 words
+__host__ __device__ constexpr long long rs_status_words(long long rows) { return rs_status_flag_words(rows) + (rows + 2 * rs_status_groups(rows)) * 512; }
+__host__ __device__ inline RsStatus rs_status_carve(uint32_t* base, long long rows, int stride) {
+    RsStatus st;
+    const long long g = rs_status_groups(rows);
+    st.tile_flag = base; st.group_cnt = base + rows; st.group_flag = st.group_cnt + g; st.ckpt_flag = st.group_flag + g;
+    st.flag_words = rs_status_flag_words(rows);
+    st.agg = base + st.flag_words; st.group = st.agg + rows * stride; st.ckpt = st.group + g * stride;
+    return st;
+}
+__device__ __forceinline__ void st_cg_u32(uint32_t* p, uint32_t v) { asm volatile("st.global.cg.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
+// Exclusive prefixes (over all tiles in front of `tile`) of the DPT digits of this thread.  total[]: this tile's counts.
+// Called by all threads of the CTA; contains barriers.
+template <int DPT, int BINS>
+__device__ __forceinline__ void tile_prefix(const RsStatus& st, long long tile, long long n_tiles, int stride, uint32_t mask,
+                                            const uint32_t (&total)[DPT], uint32_t (&prefix)[DPT], uint32_t* s_word) {
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const long long g = tile / RS_GROUP;
+    const int r = (int)(tile - g * RS_GROUP);
+    const long long g_first = g * RS_GROUP;
+    const int gsize = (int)((n_tiles - g_first < RS_GROUP) ? (n_tiles - g_first) : RS_GROUP);
+    bool exists[DPT];
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) {
+        const int d = t * DPT + j;
+        exists[j] = d < BINS && (uint32_t)d <= mask;  // digits above the mask do not exist in this pass
+        if (exists[j]) st_cg_u32(st.agg + tile * stride + d, total[j]);
+        prefix[j] = 0;
+    }
+    __threadfence();
+    __syncthreads();
+    if (t == 0) {
+        st_volatile_u32(st.tile_flag + tile, 1u);
+        s_word[0] = (atomicAdd(st.group_cnt + g, 1u) == (uint32_t)(gsize - 1)) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (s_word[0]) {  // this tile completes its group: every row of the group is published (counter after fence)
+        __threadfence();
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) {
+            if (exists[j]) {
+                const int d = t * DPT + j;
+                uint32_t sum = 0;
+#pragma unroll 4
+                for (int i = 0; i < gsize; ++i) sum += ld_volatile_u32(st.agg + (g_first + i) * stride + d);
+                st_cg_u32(st.group + g * stride + d, sum);
+            }
+        }
+        __threadfence();
+        __syncthreads();
+        if (t == 0) st_volatile_u32(st.group_flag + g, 1u);
+    }
+    if (tile == 0) return;  // block-uniform
+    // ---- warp 0: wait for the rows this tile needs; result: the checkpoint group gp (0 = the start of the keys)
+    if (warp == 0) {
+        while (r > 0) {  // the tiles in front of this one in its group
+            const uint32_t f = (lane < r) ? ld_volatile_u32(st.tile_flag + g_first + lane) : 1u;
+            if (__all_sync(0xffffffffu, f != 0u)) break;
+            __nanosleep(100);
+        }
+        long long gp = 0;
+        if (g > 0) {
+            while (true) {
+                // lane l looks at group h = g - l: is its checkpoint there, is its GROUP row there (needed for h < g)
+                const long long h = g - lane;
+                const bool ck = (h == 0) || (h > 0 && ld_volatile_u32(st.ckpt_flag + h) != 0u);
+                const bool gr = (lane == 0) || (h >= 0 && ld_volatile_u32(st.group_flag + h) != 0u);
+                const uint32_t ckm = __ballot_sync(0xffffffffu, ck);
+                const uint32_t grm = __ballot_sync(0xffffffffu, gr);
+                if (ckm) {
+                    const int l = __ffs(ckm) - 1;                       // nearest checkpoint: group g - l
+                    const uint32_t need = (l >= 31) ? 0xffffffffu : ((2u << l) - 1u);  // GROUP rows of g-1 .. g-l
+                    if ((grm & need) == need) { gp = g - l; break; }
+                }
+                __nanosleep(100);
+            }
+        }
+        if (lane == 0) s_word[1] = (uint32_t)gp;
+    }
+    __syncthreads();
+    __threadfence();
+    const long long gp = s_word[1];
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) {
+        if (exists[j]) {
+            const int d = t * DPT + j;
+            uint32_t sum = (gp > 0) ? ld_volatile_u32(st.ckpt + gp * stride + d) : 0u;
+#pragma unroll 4
+            for (long long h = gp; h < g; ++h) sum += ld_volatile_u32(st.group + h * stride + d);
+#pragma unroll 4
+            for (int i = 0; i < r; ++i) sum += ld_volatile_u32(st.agg + (g_first + i) * stride + d);
+            prefix[j] = sum;
+        }
+    }
+    if (r == 0) {  // first tile of a group: its exclusive prefix is the checkpoint of the group
+#pragma unroll
+        for (int j = 0; j < DPT; ++j)
+            if (exists[j]) st_cg_u32(st.ckpt + g * stride + t * DPT + j, prefix[j]);
+        __threadfence();
+        __syncthreads();
+        if (t == 0) st_volatile_u32(st.ckpt_flag + g, 1u);
+    }
+}
+
 // exclusive scan of one value per thread over a 256-thread block; returns the exclusive prefix and the
 // block total via *total.  s_tmp: RS_WARPS + 1 words.
 __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* s_tmp, uint32_t* total) {
@@ -147,7 +295,7 @@ template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const KeyT* __restrict__ keys, long long n_host,
                                                        const uint32_t* __restrict__ n_dev, long long capacity,
                                                        RsPasses passes, uint32_t* __restrict__ hist,
-                                                       uint32_t* __restrict__ status0, int tile_items) {
+                                                       uint32_t* __restrict__ status0, long long clear_words) {
     __shared__ uint32_t s_hist[8 * 256];
     long long n = n_dev ? (long long)(*n_dev) : n_host;
     if (n > capacity) n = capacity;
@@ -208,8 +356,7 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const KeyT* __restrict__
         if (c) atomicAdd(&hist[i], c);
     }
     // clear the look-back rows the first pass will use
-    const long long rows = (n + tile_items - 1) / tile_items;
-    for (long long i = (long long)blockIdx.x * RS_THREADS + threadIdx.x; i < rows * 256; i += stride) status0[i] = 0;
+    for (long long i = (long long)blockIdx.x * RS_THREADS + threadIdx.x; i < clear_words; i += stride) status0[i] = 0;
 }
 
 template <typename KeyT, int ITEMS, bool IDENTITY_VALS>
@@ -322,54 +469,81 @@ __global__ void __launch_bounds__(RS_THREADS, (ITEMS <= 8 ? 5 : 3)) k_rs_pass(co
     }
 }
 
-// ---- k_rs_pass2: the same pass over SUPER-TILES of S sub-tiles ------------------------------------
-// clock64 phase timing of k_rs_pass showed 40 % of a pass waiting in the look-back: the persistent CTAs
-// run in lock step, so in every wave the inclusive prefix has to cross all ~444 tiles in flight before the
-// last of them can write, and that chain repeats every wave.  Its total length is (tiles) / sqrt(tiles
-// in flight), so the cure is fewer, larger tiles without fewer CTAs: a CTA ranks S sub-tiles one after
-// the other, parks each one tile-sorted in shared memory (the registers are free again for the next),
-// publishes ONE count row for all of them and does ONE look-back.  S = 2 uses the shared memory three
-// CTAs per SM can have (2 x 32 KB staging each) and halves the chain.
-template <int ITEMS, int S, bool IDENTITY_VALS>
-__global__ void __launch_bounds__(RS_THREADS, 3) k_rs_pass2(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
+// ---- k_rs_pass3: the 32-bit-key pass over SUPER-TILES of S sub-tiles, digits of up to 9 bits -------------------------
+// clock64 phase timing of k_rs_pass showed 40 % of a pass waiting in the look-back: the persistent CTAs run in lock
+// step, so in every wave the inclusive prefix has to cross all ~444 tiles in flight before the last of them can
+// write, and that chain repeats every wave.  Its total length is (tiles) / sqrt(tiles in flight), so the cure is
+// fewer, larger tiles without fewer CTAs: a CTA ranks S sub-tiles one after the other, parks each one tile-sorted in
+// shared memory (the registers are free again for the next), publishes ONE count row for all of them and does ONE
+// look-back.
+//   BITS  : digit width of the template instance (ballot rounds, bins); a pass with fewer bits uses the next instance
+//           up (its upper ballots agree on every lane).  Thread t owns digits [t * DPT, (t + 1) * DPT).
+//   partial sub-tiles: a warp owns ITEMS * 32 consecutive keys of a sub-tile; warps whose chunk lies behind the end of
+//           the span skip the ranking altogether (a warp-uniform branch around the whole phase - per-item guards
+//           were measured 1.5x slower: they cut the unrolled ballot chains into basic blocks).
+//   DROP  : the compacting first pass of the frame's depth sort: keys equal to 0xFFFFFFFF (culled Gaussians) are
+//           neither counted nor written, the others leave as key' = min(max(key, k0), khi) - k0, which makes the
+//           visible depth range a 27-bit integer (three 9-bit passes over the visible Gaussians instead of four 8-bit
+//           passes over all of them).
+struct RsRebase { uint32_t k0, khi; };
+
+template <int BITS, int ITEMS, int S, int MINB, bool IDENTITY_VALS, bool DROP>
+__global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                                                           const uint32_t* __restrict__ vals_in,
                                                           uint32_t* __restrict__ vals_out, long long n_host,
                                                           const uint32_t* __restrict__ n_dev, long long capacity,
                                                           int shift, int bits, const uint32_t* __restrict__ hist,
                                                           uint32_t* __restrict__ ticket, uint32_t* __restrict__ status_cur,
-                                                          uint32_t* __restrict__ status_next, int mix, int balance) {
-    constexpr int TILE = RS_THREADS * ITEMS;  // one sub-tile
+                                                          uint32_t* __restrict__ status_next, int row_stride, int span_max,
+                                                          long long status_rows, RsRebase rb) {
+    constexpr int BINS = 1 << BITS;
+    constexpr int DPT = (BINS + RS_THREADS - 1) / RS_THREADS;  // digits per thread in the per-digit phases
     extern __shared__ __align__(16) unsigned char s_dyn[];
-    uint32_t* s_keys = reinterpret_cast<uint32_t*>(s_dyn);  // [S][TILE] tile-sorted keys
-    uint32_t* s_vals = s_keys + S * TILE;                   // [S][TILE]
-    __shared__ uint16_t s_whist[RS_WARPS][256];  // per-warp digit counts (<= 32 * ITEMS each)
-    __shared__ uint32_t s_digit_start[256];
-    __shared__ uint32_t s_bin_base[S][256];
-    __shared__ uint32_t s_global_excl[256];
+    uint32_t* s_keys = reinterpret_cast<uint32_t*>(s_dyn);    // [span_max] tile-sorted keys, sub-tile after sub-tile
+    uint32_t* s_vals = s_keys + span_max;                     // [span_max]
+    __shared__ __align__(16) uint16_t s_whist[RS_WARPS * BINS];  // per-warp digit counts (<= 32 * ITEMS each)
+    __shared__ uint16_t s_digit_start[BINS];
+    __shared__ uint32_t s_bin_base[S][BINS];
     __shared__ uint32_t s_tmp[RS_WARPS + 1];
     __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_word[2];
+    const RsStatus st = rs_status_carve(status_cur, status_rows, row_stride);
+    const long long next_flag_words = rs_status_flag_words(status_rows);
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const bool no_lookback = (bits & 0x100) != 0;  // timing experiments only (GSR_DEBUG_NO_LOOKBACK)
+    bits &= 0xff;
     const uint32_t mask = (1u << bits) - 1u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     pdl_wait();  // resident behind the previous pass; nothing of global memory is touched before this
     long long n = n_dev ? (long long)(*n_dev) : n_host;
     if (n > capacity) n = capacity;
 
-    s_global_excl[t] = block_excl_scan_256(hist[t], s_tmp, nullptr);
-
-    // Balanced spans: a super-tile covers `span` <= S * TILE items, chosen so that every CTA of the grid gets the
-    // same number of equally long super-tiles.  With the full 8192-item span 3 M keys are 367 super-tiles on 444
-    // CTA slots - SMs holding three of them rank 1.5x longer than SMs holding two, and in a single-wave pass
-    // everybody's look-back waits for the slowest count row.
-    long long span = (long long)S * TILE;
-    if (balance) {
-        const long long G = gridDim.x;
-        const long long waves = (n + G * span - 1) / (G * span);
-        long long sp = (n + G * waves - 1) / (G * (waves > 0 ? waves : 1));
-        sp = (sp + 31) & ~31ll;  // 128-byte aligned warp loads
-        span = sp < TILE ? TILE : (sp > span ? span : sp);  // >= TILE: the cleared look-back rows are n / TILE
+    // exclusive scan of the pass's global digit counts; thread t keeps the bases of its own digits
+    uint32_t gexcl[DPT];
+    {
+        uint32_t loc[DPT], sum = 0;
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) {
+            const int d = t * DPT + j;
+            loc[j] = (d < BINS) ? hist[d] : 0u;
+            sum += loc[j];
+        }
+        uint32_t run = block_excl_scan_256(sum, s_tmp, nullptr);
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) { gexcl[j] = run; run += loc[j]; }
     }
+
+    // Balanced spans: every CTA of the grid gets the same number of equally long super-tiles (with fixed spans 3 M
+    // keys are 367 super-tiles on 444 CTA slots, and in a single-wave pass everybody's look-back waits for the
+    // slowest count row).
+    const long long G = gridDim.x;
+    const long long waves = (n + G * span_max - 1) / (G * span_max);
+    long long span = (n + G * waves - 1) / (G * (waves > 0 ? waves : 1));
+    span = (span + 31) & ~31ll;  // 128-byte aligned warp loads
+    if (span > span_max) span = span_max;
+    if (span < 256) span = 256;
+    const long long n_tiles = (n + span - 1) / span;
 
     while (true) {
         if (t == 0) s_tile = atomicAdd(ticket, 1u);
@@ -378,151 +552,271 @@ __global__ void __launch_bounds__(RS_THREADS, 3) k_rs_pass2(const uint32_t* __re
         const long long super_base = tile * span;
         if (super_base >= n) break;
         const long long super_end = (super_base + span < n) ? super_base + span : n;
-        status_next[tile * 256 + t] = 0;
-        uint32_t cnt[S], dst[S];  // digit t of sub-tile s: valid count, start inside the sorted sub-tile
-        int n_valid[S];
+        for (long long j = tile * RS_THREADS + t; j < next_flag_words; j += n_tiles * RS_THREADS) status_next[j] = 0;  // flags of the next pass
+        constexpr int per_sub = ITEMS * RS_THREADS;
+        uint32_t cnt[S][DPT];   // digit d of sub-tile s: keys
+        int sub_out[S];         // keys parked by sub-tile s
+        int out_base = 0;       // start of the sub-tile in the staging area
 #pragma unroll
         for (int sub = 0; sub < S; ++sub) {
-            const long long tile_base = super_base + (long long)sub * TILE;
-            n_valid[sub] = (int)((super_end - tile_base < TILE) ? ((super_end - tile_base > 0) ? (super_end - tile_base) : 0) : TILE);
-            cnt[sub] = 0; dst[sub] = 0;
-            if (n_valid[sub] == 0) continue;  // block-uniform
+            const long long sub_base = super_base + (long long)sub * per_sub;
+            const long long sub_end = (sub_base + per_sub < super_end) ? sub_base + per_sub : super_end;
 #pragma unroll
-            for (int w = 0; w < RS_WARPS; ++w) s_whist[w][t] = 0;
+            for (int j = 0; j < DPT; ++j) cnt[sub][j] = 0;
+            sub_out[sub] = 0;
+            if (sub_base >= super_end) continue;  // block-uniform
+            for (int i = t; i < RS_WARPS * BINS / 8; i += RS_THREADS) reinterpret_cast<uint4*>(s_whist)[i] = make_uint4(0u, 0u, 0u, 0u);
             __syncthreads();
-            // ---- load (warp-striped: item i of lane l is element warp_base + i*32 + l)
+            // ---- load (warp-striped: item i of lane l is element warp_first + i*32 + l; 32-bit offsets from one pointer)
             uint32_t key[ITEMS], val[ITEMS];
-            const long long warp_base = tile_base + (long long)warp * (32 * ITEMS);
+            const long long warp_first = sub_base + (long long)warp * (ITEMS * 32);
+            const bool warp_has_keys = warp_first < sub_end;  // warp-uniform
+            // items i with i * 32 < left hold a key of the sub-tile
+            const int left = (int)((sub_end - warp_first < (long long)(ITEMS * 32)) ? (sub_end - warp_first) : (long long)(ITEMS * 32)) - lane;
+            const uint32_t* kp = keys_in + warp_first + lane;
+            const uint32_t* vp = IDENTITY_VALS ? nullptr : vals_in + warp_first + lane;
+            const uint32_t idx0 = (uint32_t)warp_first + (uint32_t)lane;
+            uint32_t vbits = 0;  // DROP only: bit i = item i takes part (a key that is not dropped)
 #pragma unroll
             for (int i = 0; i < ITEMS; ++i) {
-                const long long idx = warp_base + i * 32 + lane;
-                const bool valid = idx < super_end;
-                key[i] = valid ? keys_in[idx] : 0xFFFFFFFFu;
-                if (IDENTITY_VALS) val[i] = (uint32_t)idx;
-                else val[i] = valid ? vals_in[idx] : 0u;
-            }
-            // ---- rank inside the warp, digit counters per warp.  All matches first: they are independent of the
-            // counters, so their ballots overlap the serial counter updates below (0.232 -> 0.226 ms per tile
-            // sort).  `mix` sends odd items through the hardware MATCH.ANY instead, to use the otherwise idle
-            // address-divergence unit next to the ALU pipe: measured SLOWER (0.240 ms), the unit is shared by the SM.
-            uint32_t rank[ITEMS];  // first the peer mask, then the rank
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i) {
-                const uint32_t d = (key[i] >> shift) & mask;
-                rank[i] = (mix && (i & 1)) ? __match_any_sync(0xffffffffu, d) : match_digit(d, bits);
-            }
-#pragma unroll
-            for (int i = 0; i < ITEMS; ++i) {
-                const uint32_t d = (key[i] >> shift) & mask;
-                const uint32_t peers = rank[i];
-                const int leader = __ffs(peers) - 1;
-                uint32_t old = 0;
-                if (lane == leader) {
-                    old = s_whist[warp][d];
-                    s_whist[warp][d] = (uint16_t)(old + __popc(peers));
+                const bool in = i * 32 < left;
+                key[i] = in ? kp[i * 32] : 0xFFFFFFFFu;  // padding keys: digit `mask` of every pass, behind the valid keys
+                if (IDENTITY_VALS) val[i] = idx0 + i * 32;
+                else val[i] = in ? vp[i * 32] : 0u;
+                if (DROP) {
+                    const bool keep = in && (key[i] != 0xFFFFFFFFu);
+                    key[i] = min(max(key[i], rb.k0), rb.khi) - rb.k0;
+                    vbits |= (keep ? 1u : 0u) << i;
                 }
-                old = __shfl_sync(0xffffffffu, old, leader);
-                rank[i] = old + __popc(peers & lt_mask);
-                __syncwarp();
+            }
+            // padding keys that get counted: those of the warps that hold at least one key of the sub-tile
+            const int n_sub = (int)(sub_end - sub_base);
+            const int n_pad = ((n_sub + ITEMS * 32 - 1) / (ITEMS * 32)) * (ITEMS * 32) - n_sub;
+            // ---- rank inside the warp, digit counters per warp.  All matches first: they are independent of the
+            // counters, so their ballots overlap the serial counter updates below.  The update is branch free: every
+            // lane reads its digit's counter (a broadcast among peers), the lowest peer writes it back.
+            uint32_t rank[ITEMS];  // first the peer mask, then the rank
+            if (warp_has_keys) {
+                uint16_t* wh = s_whist + warp * BINS;
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i) {
+                    const uint32_t d = (key[i] >> shift) & mask;
+                    uint32_t m = match_digit_t<BITS>(d);
+                    if (DROP) m &= __ballot_sync(0xffffffffu, (vbits >> i) & 1u);
+                    rank[i] = m;
+                }
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i) {
+                    const uint32_t d = (key[i] >> shift) & mask;
+                    const uint32_t peers = rank[i];
+                    const uint32_t below = peers & lt_mask;
+                    const uint32_t old = wh[d];
+                    __syncwarp();  // every peer has read the counter
+                    if (below == 0u && (!DROP || ((vbits >> i) & 1u))) wh[d] = (uint16_t)(old + __popc(peers));
+                    __syncwarp();  // the update is visible to the next item's reads
+                    rank[i] = old + __popc(below);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < ITEMS; ++i) rank[i] = 0;
             }
             __syncthreads();
-            // ---- per digit (thread t owns digit t): exclusive scan over warps, sub-tile count
-            uint32_t count = 0;
+            // ---- per digit (thread t owns digits t * DPT ...): exclusive scan over warps, sub-tile count
+            uint32_t loc[DPT], sum = 0;
 #pragma unroll
-            for (int w = 0; w < RS_WARPS; ++w) {
-                const uint32_t c = s_whist[w][t];
-                s_whist[w][t] = (uint16_t)count;
-                count += c;
+            for (int j = 0; j < DPT; ++j) {
+                const int d = t * DPT + j;
+                uint32_t count = 0;
+                if (d < BINS) {
+#pragma unroll
+                    for (int w = 0; w < RS_WARPS; ++w) {
+                        const uint32_t c = s_whist[w * BINS + d];
+                        s_whist[w * BINS + d] = (uint16_t)count;
+                        count += c;
+                    }
+                }
+                loc[j] = count; sum += count;
+                // padding keys (all ones) sit in digit `mask`, behind every valid key of that digit (not in the
+                // compacting pass: it counts only the keys that take part)
+                cnt[sub][j] = count - ((!DROP && (uint32_t)d == mask) ? (uint32_t)n_pad : 0u);
             }
-            // padding keys (all ones) sit in digit `mask`, after every valid key of that digit
-            cnt[sub] = count - (((uint32_t)t == mask) ? (uint32_t)(TILE - n_valid[sub]) : 0u);
-            const uint32_t dstart = block_excl_scan_256(count, s_tmp, nullptr);
-            dst[sub] = dstart;
-            s_digit_start[t] = dstart;
+            uint32_t total = 0;
+            uint32_t run = block_excl_scan_256(sum, s_tmp, &total);
+            sub_out[sub] = DROP ? (int)total : n_sub;
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                const int d = t * DPT + j;
+                if (d < BINS) {
+                    s_digit_start[d] = (uint16_t)run;
+                    s_bin_base[sub][d] = 0u - run;  // completed below once the look-back is done
+                }
+                run += loc[j];
+            }
             __syncthreads();
             // ---- park the sub-tile in shared memory in tile-sorted order
-            uint32_t* sk = s_keys + sub * TILE;
-            uint32_t* sv = s_vals + sub * TILE;
+            uint32_t* sk = s_keys + out_base;
+            uint32_t* sv = s_vals + out_base;
+            if (warp_has_keys) {
+                const uint16_t* wh = s_whist + warp * BINS;
 #pragma unroll
-            for (int i = 0; i < ITEMS; ++i) {
-                const uint32_t d = (key[i] >> shift) & mask;
-                const uint32_t pos = s_digit_start[d] + s_whist[warp][d] + rank[i];
-                sk[pos] = key[i];
-                sv[pos] = val[i];
+                for (int i = 0; i < ITEMS; ++i) {
+                    if (!DROP || ((vbits >> i) & 1u)) {  // (padding keys park behind the valid ones and are never written out)
+                        const uint32_t d = (key[i] >> shift) & mask;
+                        const uint32_t pos = (uint32_t)s_digit_start[d] + wh[d] + rank[i];
+                        sk[pos] = key[i];
+                        sv[pos] = val[i];
+                    }
+                }
             }
+            out_base += sub_out[sub];
             __syncthreads();  // s_whist / s_digit_start are rewritten by the next sub-tile
         }
-        // ---- one count row and one look-back for the whole super-tile
-        uint32_t total = 0;
+        // ---- one count row for the whole super-tile, then its prefix over the tiles in front (tile_prefix)
+        uint32_t total[DPT], prefix[DPT];
 #pragma unroll
-        for (int sub = 0; sub < S; ++sub) total += cnt[sub];
-        uint32_t prefix = 0;
-        if ((uint32_t)t <= mask) {  // digits above the mask do not exist in this pass
-            if (tile == 0) st_volatile_u32(&status_cur[t], RS_FLAG_INC | total);
-            else {
-                st_volatile_u32(&status_cur[tile * 256 + t], RS_FLAG_AGG | total);
-                prefix = look_back(status_cur, tile, t);
-                st_volatile_u32(&status_cur[tile * 256 + t], RS_FLAG_INC | (prefix + total));
-            }
+        for (int j = 0; j < DPT; ++j) {
+            total[j] = 0;
+#pragma unroll
+            for (int sub = 0; sub < S; ++sub) total[j] += cnt[sub][j];
+            prefix[j] = 0;
         }
-        uint32_t run = s_global_excl[t] + prefix;
+        if (!no_lookback) tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix, s_word);
 #pragma unroll
-        for (int sub = 0; sub < S; ++sub) {
-            s_bin_base[sub][t] = run - dst[sub];
-            run += cnt[sub];
+        for (int j = 0; j < DPT; ++j) {
+            const int d = t * DPT + j;
+            if (d < BINS) {
+                uint32_t run = gexcl[j] + prefix[j];
+#pragma unroll
+                for (int sub = 0; sub < S; ++sub) {
+                    s_bin_base[sub][d] += run;
+                    run += cnt[sub][j];
+                }
+            }
         }
         __syncthreads();
         // ---- contiguous runs per digit go out to global memory
+        int base = 0;
 #pragma unroll
         for (int sub = 0; sub < S; ++sub) {
-            const uint32_t* sk = s_keys + sub * TILE;
-            const uint32_t* sv = s_vals + sub * TILE;
-            for (int s = t; s < n_valid[sub]; s += RS_THREADS) {
+            const uint32_t* sk = s_keys + base;
+            const uint32_t* sv = s_vals + base;
+            for (int s = t; s < sub_out[sub]; s += RS_THREADS) {
                 const uint32_t k = sk[s];
                 const uint32_t d = (k >> shift) & mask;
                 const uint32_t o = s_bin_base[sub][d] + (uint32_t)s;
                 if (keys_out) keys_out[o] = k;
                 vals_out[o] = sv[s];
             }
+            base += sub_out[sub];
         }
         __syncthreads();  // staging and s_bin_base are rewritten by the next super-tile
     }
 }
 
-int g_num_sms = 0;
-int num_sms() {
-    if (g_num_sms == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        if (g_num_sms <= 0) g_num_sms = 148;
+int num_sms() {  // of the CURRENT device (a process may hold handles on several)
+    static int cache[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (cache[dev] == 0) {
+        cudaDeviceGetAttribute(&cache[dev], cudaDevAttrMultiProcessorCount, dev);
+        if (cache[dev] <= 0) cache[dev] = 148;
     }
-    return g_num_sms;
+    return cache[dev];
 }
+
+// ---- k_rs_pass3 configuration: 15 keys per thread and sub-tile, two sub-tiles, three CTAs per SM -----------------
+// 9-bit digits: 13 KB of counters per CTA leave 60 KB of staging (15 keys per thread); up to 8 bits: 16 keys
+constexpr int RS3_S = 2, RS3_MINB = 3;
+constexpr int rs3_items(int bits) { return bits > 8 ? 15 : 16; }
+constexpr int rs3_span(int bits) { return RS3_S * rs3_items(bits) * RS_THREADS; }  // 7680 / 8192 keys
+constexpr int RS3_SPAN_MIN = rs3_span(9);
+
+template <int BITS, bool IDENT, bool DROP>
+void rs3_launch(unsigned grid, cudaStream_t stream, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
+                long long n_host, const uint32_t* n_dev, long long capacity, int shift, int bits, const uint32_t* hist,
+                uint32_t* ticket, uint32_t* st_cur, uint32_t* st_next, int row_stride, int span_max, long long status_rows,
+                RsRebase rb) {
+    launch_pdl_m(1, k_rs_pass3<BITS, rs3_items(BITS), RS3_S, RS3_MINB, IDENT, DROP>, dim3(grid), dim3(RS_THREADS),
+                 (size_t)rs3_span(BITS) * 8, stream, kin, kout, vin, vout, n_host, n_dev, capacity, shift, bits, hist, ticket, st_cur,
+                 st_next, row_stride, span_max, status_rows, rb);
+}
+template <int BITS, bool IDENT, bool DROP>
+bool rs3_prepare_one() {
+    const void* f = (const void*)k_rs_pass3<BITS, rs3_items(BITS), RS3_S, RS3_MINB, IDENT, DROP>;
+    return cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, rs3_span(BITS) * 8) == cudaSuccess &&
+           cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess;
+}
+int g_rs3_ctas[64] = {};  // resident CTAs per SM of the pass kernel, per device (0 = not prepared yet)
 
 }  // namespace
 
-void set_sort_small_tiles(int v) { g_rs_small = v ? 1 : 0; }
-void set_sort_prefetch(int v) { g_rs_prefetch = v ? 1 : 0; }
-void set_sort_mix(int v) { g_rs_mix = v ? 1 : 0; }
-void set_sort_balance(int v) { g_rs_balance = v ? 1 : 0; }
-
-size_t sort_scratch_bytes(long long max_items, int key_bytes) {
-    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::SMALL : RsCfg<uint32_t>::SMALL;
-    const long long tiles = (max_items + RS_THREADS * items - 1) / (RS_THREADS * items) + 1;
-    return (size_t)(8 * 256 + 64) * 4 + 2 * (size_t)tiles * 256 * 4;
+// Opt-ins of the pass kernels (dynamic shared memory above 48 KB) for the CURRENT device; gsr_create calls this
+// for every handle, so a process with handles on several GPUs configures each of them.
+int radix_sort_prepare_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return -1;
+    bool ok = true;
+    ok = rs3_prepare_one<5, false, false>() && ok;
+    ok = rs3_prepare_one<6, false, false>() && ok;
+    ok = rs3_prepare_one<7, false, false>() && ok;
+    ok = rs3_prepare_one<8, false, false>() && ok;
+    ok = rs3_prepare_one<9, false, false>() && ok;
+    ok = rs3_prepare_one<8, true, false>() && ok;
+    ok = rs3_prepare_one<9, true, false>() && ok;
+    ok = rs3_prepare_one<8, true, true>() && ok;
+    ok = rs3_prepare_one<9, true, true>() && ok;
+    int nb = 0;
+    if (!ok || cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rs_pass3<9, rs3_items(9), RS3_S, RS3_MINB, false, false>, RS_THREADS,
+                                                             (size_t)rs3_span(9) * 8) != cudaSuccess || nb <= 0) {
+        cudaGetLastError();
+        return -1;
+    }
+    g_rs3_ctas[dev] = nb;
+    return 0;
 }
 
-void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int key_bytes) {
-    const int items = (key_bytes == 8) ? RsCfg<uint64_t>::SMALL : RsCfg<uint32_t>::SMALL;
-    const long long tiles = (max_items + RS_THREADS * items - 1) / (RS_THREADS * items) + 1;
+namespace {
+int rs3_ctas_per_sm() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return 1;
+    if (g_rs3_ctas[dev] == 0) radix_sort_prepare_device();
+    return g_rs3_ctas[dev] > 0 ? g_rs3_ctas[dev] : 1;
+}
+// grid and look-back rows of a pass3 sort over at most `upper` keys in spans of at most span_max keys
+void rs3_shape(long long upper, int span_max, long long* grid, long long* rows) {
+    const long long resident = (long long)num_sms() * rs3_ctas_per_sm();
+    long long g = (upper + 2047) / 2048;  // never more CTAs than 2048-key spans
+    if (g > resident) g = resident;
+    if (g > 3 * 192) g = 3 * 192;  // what scratch_rows provides for
+    if (g < 1) g = 1;
+    const long long waves = (upper + g * span_max - 1) / (g * span_max);
+    *grid = g;
+    *rows = g * (waves > 0 ? waves : 1) + 1;
+}
+}  // namespace
+
+// Look-back rows: the buffers are sized in rows of RS_ROW_WORDS words.  A 32-bit-key sort over max_items keys uses at
+// most max_items / 7680 + resident CTAs + 1 rows of 256 or 512 words (rs3_shape), a 64-bit-key sort max_items / 3072
+// rows of 256 words.
+constexpr int RS_ROW_WORDS = 512;
+constexpr long long scratch_rows(long long max_items) { return max_items / 6144 + 3 * 192 + 4; }  // 3 resident CTAs per SM, <= 192 SMs
+
+size_t sort_scratch_bytes(long long max_items, int /*key_bytes*/) {
+    return (size_t)(8 * 256 + 64) * 4 + 2 * (size_t)rs_status_words(scratch_rows(max_items)) * 4;
+}
+
+void sort_scratch_carve(SortScratch* s, void* base, long long max_items, int /*key_bytes*/) {
+    const long long rows = scratch_rows(max_items);
     uint32_t* p = reinterpret_cast<uint32_t*>(base);
     s->hist = p;
     s->tickets = p + 8 * 256;
     s->zero_bytes = (size_t)(8 * 256 + 64) * 4;
     s->status[0] = p + 8 * 256 + 64;
-    s->status[1] = s->status[0] + (size_t)tiles * 256;
-    s->max_tiles = tiles;
+    s->status[1] = s->status[0] + (size_t)rs_status_words(rows);
+    s->max_tiles = rows;
 }
 
 template <typename KeyT, int ITEMS>
@@ -537,88 +831,85 @@ void launch_pass(bool identity, unsigned grid, cudaStream_t stream, const KeyT* 
                                                                       bits, hist, ticket, st_cur, st_next);
 }
 
-// super-tile variant (32-bit keys): dynamic shared memory = S staged sub-tiles of keys + values
-constexpr int RS2_ITEMS = 16, RS2_S = 2;
-constexpr size_t RS2_SMEM = (size_t)RS2_S * RS_THREADS * RS2_ITEMS * (sizeof(uint32_t) + sizeof(uint32_t));
-int rs2_ctas_per_sm() {  // 0 = the variant cannot run here
-    static int n = -1;
-    if (n < 0) {
-        n = 0;
-        bool ok = true;
-        auto prep = [&](const void* f) {
-            ok = ok && cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS2_SMEM) == cudaSuccess;
-            ok = ok && cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess;
-        };
-        prep((const void*)k_rs_pass2<RS2_ITEMS, RS2_S, true>);
-        prep((const void*)k_rs_pass2<RS2_ITEMS, RS2_S, false>);
-        int nb = 0;
-        if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rs_pass2<RS2_ITEMS, RS2_S, false>, RS_THREADS,
-                                                                RS2_SMEM) == cudaSuccess)
-            n = nb;
-        cudaGetLastError();
-    }
-    return n;
+// words per look-back row of a sort: 512 when a pass has 9-bit digits, else 256
+static int plan_row_stride(const SortOptions* opt) {
+    if (opt && opt->n_pass > 0)
+        for (int p = 0; p < opt->n_pass; ++p) if (opt->pass_bits[p] > 8) return 512;
+    return 256;
 }
 
 template <typename KeyT>
-void sort_scratch_clear(SortScratch* scratch, long long upper, bool hist_ready, cudaStream_t stream) {
+void sort_scratch_clear(SortScratch* scratch, long long upper, bool hist_ready, cudaStream_t stream, const SortOptions* opt) {
     if (upper <= 0) return;
     if (hist_ready) {
-        // the digit histograms come from the caller (k_tile_scan): clear the tickets and the look-back rows of
-        // the first pass only
-        const int TILE = RS_THREADS * (g_rs_small ? RsCfg<KeyT>::SMALL : RsCfg<KeyT>::LARGE);
-        const long long tiles_upper = (upper + TILE - 1) / TILE;
+        // the digit histograms come from the caller (k_preprocess / k_tile_scan): clear the tickets and the look-back
+        // rows of the first pass only
+        // 32-bit keys: the flag words of the first pass (k_rs_pass3); 64-bit keys: its look-back rows (k_rs_pass)
+        size_t words;
+        if (sizeof(KeyT) == 4) words = (size_t)rs_status_flag_words(scratch->max_tiles);
+        else words = (size_t)((upper + RS_THREADS * RsCfg<KeyT>::LARGE - 1) / (RS_THREADS * RsCfg<KeyT>::LARGE)) * 256;
         cudaMemsetAsync(scratch->tickets, 0, 64 * sizeof(uint32_t), stream);
-        cudaMemsetAsync(scratch->status[0], 0, (size_t)tiles_upper * 256 * sizeof(uint32_t), stream);
+        cudaMemsetAsync(scratch->status[0], 0, words * sizeof(uint32_t), stream);
     } else {
         cudaMemsetAsync(scratch->hist, 0, scratch->zero_bytes, stream);  // histograms + tickets; k_rs_hist clears the rows
     }
 }
-template void sort_scratch_clear<uint32_t>(SortScratch*, long long, bool, cudaStream_t);
-template void sort_scratch_clear<uint64_t>(SortScratch*, long long, bool, cudaStream_t);
+template void sort_scratch_clear<uint32_t>(SortScratch*, long long, bool, cudaStream_t, const SortOptions*);
+template void sort_scratch_clear<uint64_t>(SortScratch*, long long, bool, cudaStream_t, const SortOptions*);
 
 template <typename KeyT>
 int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, bool vals_identity,
                      long long n_host, const uint32_t* n_dev, long long capacity, int begin_bit, int end_bit,
                      SortScratch* scratch, cudaStream_t stream, long long* launch_count, const SortOptions* opt) {
-    const int first_bits = (opt && opt->first_bits > 0) ? opt->first_bits : 8;
     const bool hist_ready = opt && opt->hist_ready;
     const bool vals_only_last = opt && opt->vals_only_last;
+    const bool drop = opt && opt->drop_rebase;
     RsPasses passes;
     passes.n = 0;
     passes.direct_mask = opt ? opt->hist_direct_mask : 0u;
-    for (int b = begin_bit; b < end_bit && passes.n < 8;) {
-        const int want = (passes.n == 0) ? first_bits : 8;
-        passes.shift[passes.n] = b;
-        passes.bits[passes.n] = (end_bit - b < want) ? (end_bit - b) : want;
-        b += passes.bits[passes.n];
-        ++passes.n;
+    if (opt && opt->n_pass > 0) {  // explicit digit plan
+        int b = begin_bit;
+        for (int p = 0; p < opt->n_pass && p < 8; ++p) {
+            passes.shift[p] = b;
+            passes.bits[p] = opt->pass_bits[p];
+            b += opt->pass_bits[p];
+            ++passes.n;
+        }
+    } else {
+        for (int b = begin_bit; b < end_bit && passes.n < 8;) {
+            passes.shift[passes.n] = b;
+            passes.bits[passes.n] = (end_bit - b < 8) ? (end_bit - b) : 8;
+            b += passes.bits[passes.n];
+            ++passes.n;
+        }
     }
     for (int p = passes.n; p < 8; ++p) { passes.shift[p] = 0; passes.bits[p] = 1; }
     if (passes.n == 0) return 0;
     const long long upper = n_dev ? capacity : n_host;
     if (upper <= 0) return 0;
-    const bool small = g_rs_small != 0;
-    const int TILE = RS_THREADS * (small ? RsCfg<KeyT>::SMALL : RsCfg<KeyT>::LARGE);
-    const long long tiles_upper = (upper + TILE - 1) / TILE;
     const int sms = num_sms();
-    if (!(opt && opt->scratch_cleared)) sort_scratch_clear<KeyT>(scratch, upper, hist_ready, stream);
+    const int row_stride = plan_row_stride(opt);
+    const int hist_stride = (opt && opt->hist_stride > 0) ? opt->hist_stride : 256;
+    long long grid = 1, rows0 = 1;
+    const int span_max = row_stride > 256 ? rs3_span(9) : rs3_span(8);  // one span size for all passes of a sort
+    if (sizeof(KeyT) == 4) {
+        rs3_shape(upper, span_max, &grid, &rows0);
+    } else {
+        const long long tiles_upper = (upper + RS_THREADS * RsCfg<KeyT>::LARGE - 1) / (RS_THREADS * RsCfg<KeyT>::LARGE);
+        grid = tiles_upper < (long long)sms * 3 ? tiles_upper : (long long)sms * 3;
+        if (grid < 1) grid = 1;
+        rows0 = tiles_upper;
+    }
+    if (!(opt && opt->scratch_cleared)) sort_scratch_clear<KeyT>(scratch, upper, hist_ready, stream, opt);
     if (!hist_ready) {
         long long g = (upper + RS_THREADS * 8 - 1) / (RS_THREADS * 8);
         if (g > sms * 8) g = sms * 8;
         if (g < 1) g = 1;
+        const long long clear_words = (sizeof(KeyT) == 4) ? rs_status_flag_words(scratch->max_tiles) : rows0 * 256;
         k_rs_hist<KeyT><<<(unsigned)g, RS_THREADS, 0, stream>>>(keys_first, n_host, n_dev, capacity, passes, scratch->hist,
-                                                               scratch->status[0], TILE);
+                                                               scratch->status[0], clear_words);
         if (launch_count) ++*launch_count;
     }
-    // super-tile variant: 32-bit keys, default tile size
-    int pf_ctas = 0;
-    if (sizeof(KeyT) == 4 && !small && g_rs_prefetch) pf_ctas = rs2_ctas_per_sm();
-    const int per_sm = pf_ctas > 0 ? pf_ctas : (small ? 5 : 3);  // resident CTAs per SM: persistent CTAs, one wave
-    // balanced spans are never shorter than one sub-tile, so up to tiles_upper CTAs can have work
-    const long long work_tiles = pf_ctas > 0 ? (g_rs_balance ? tiles_upper : (tiles_upper + RS2_S - 1) / RS2_S) : tiles_upper;
-    long long grid = work_tiles < (long long)sms * per_sm ? work_tiles : (long long)sms * per_sm;
-    if (grid < 1) grid = 1;
     const KeyT* kin = keys_first; KeyT* kout = keys_tmp; KeyT* kother = keys;
     uint32_t* vin = vals; uint32_t* vout = vals_tmp;
     for (int p = 0; p < passes.n; ++p) {
@@ -626,25 +917,29 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
         uint32_t* st_cur = scratch->status[p & 1];
         uint32_t* st_next = scratch->status[(p + 1) & 1];
         const bool identity = (p == 0 && vals_identity);
-        if (pf_ctas > 0) {
-            if constexpr (sizeof(KeyT) == 4) {
-                if (identity)
-                    launch_pdl_m(1, k_rs_pass2<RS2_ITEMS, RS2_S, true>, dim3((unsigned)grid), dim3(RS_THREADS), RS2_SMEM, stream,
-                               kin, kout, (const uint32_t*)nullptr, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
-                               (const uint32_t*)(scratch->hist + p * 256), scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
-                else
-                    launch_pdl_m(1, k_rs_pass2<RS2_ITEMS, RS2_S, false>, dim3((unsigned)grid), dim3(RS_THREADS), RS2_SMEM, stream,
-                               kin, kout, (const uint32_t*)vin, vout, n_host, n_dev, capacity, passes.shift[p], passes.bits[p],
-                               (const uint32_t*)(scratch->hist + p * 256), scratch->tickets + p, st_cur, st_next, g_rs_mix, g_rs_balance);
-            }
-        } else if (small)
-            launch_pass<KeyT, RsCfg<KeyT>::SMALL>(identity, (unsigned)grid, stream, kin, kout, vin, vout, n_host, n_dev, capacity,
-                                                  passes.shift[p], passes.bits[p], scratch->hist + p * 256,
-                                                  scratch->tickets + p, st_cur, st_next);
-        else
+        const uint32_t* hist_p = scratch->hist + p * hist_stride;
+        if constexpr (sizeof(KeyT) == 4) {
+            const uint32_t* nd = (p > 0 && opt && opt->n_dev_rest) ? opt->n_dev_rest : n_dev;
+            static const int dbg_no_lb = getenv("GSR_DEBUG_NO_LOOKBACK") ? 0x100 : 0;
+            const int bits = passes.bits[p] | dbg_no_lb, shift = passes.shift[p];
+            const RsRebase rb = {opt ? opt->k0 : 0u, opt ? opt->khi : 0xFFFFFFFFu};
+#define RS3_GO(B, I, D) rs3_launch<B, I, D>((unsigned)grid, stream, kin, kout, vin, vout, n_host, nd, capacity, shift, bits, hist_p, \
+                                           scratch->tickets + p, st_cur, st_next, row_stride, span_max, scratch->max_tiles, rb)
+            const int nb = passes.bits[p];
+            if (p == 0 && drop) {  // compacting first pass (identity values)
+                if (nb > 8) RS3_GO(9, true, true); else RS3_GO(8, true, true);
+            } else if (identity) {
+                if (nb > 8) RS3_GO(9, true, false); else RS3_GO(8, true, false);
+            } else if (nb > 8) RS3_GO(9, false, false);
+            else if (nb == 8) RS3_GO(8, false, false);
+            else if (nb == 7) RS3_GO(7, false, false);
+            else if (nb == 6) RS3_GO(6, false, false);
+            else RS3_GO(5, false, false);
+#undef RS3_GO
+        } else {
             launch_pass<KeyT, RsCfg<KeyT>::LARGE>(identity, (unsigned)grid, stream, kin, kout, vin, vout, n_host, n_dev, capacity,
-                                                  passes.shift[p], passes.bits[p], scratch->hist + p * 256,
-                                                  scratch->tickets + p, st_cur, st_next);
+                                                  passes.shift[p], passes.bits[p], hist_p, scratch->tickets + p, st_cur, st_next);
+        }
         if (launch_count) ++*launch_count;
         kin = kout; { KeyT* tk = kout; kout = kother; kother = tk; }
         uint32_t* tv = vin; vin = vout; vout = tv;
@@ -660,13 +955,12 @@ template int radix_sort_pairs<uint64_t>(const uint64_t*, uint64_t*, uint64_t*, u
 // ---- allocation-free sort (gsr_sort_pairs_static) ---------------------------------------------------------------
 // The radix passes need scratch (digit histograms, tile tickets, two buffers of look-back rows).  Callers that must
 // not call cudaMalloc get the same sort with that scratch in a static device array of fixed size: every GPU that
-// loads libgsr.so holds RS_STATIC_WORDS * 4 bytes (about 5.6 MB) until the process exits.  All calls on a device share
+// loads libgsr.so holds RS_STATIC_WORDS * 4 bytes (about 5.8 MB) until the process exits.  All calls on a device share
 // the array; the sort clears what must start at zero (histograms + tickets by memset, the first look-back rows by the
 // histogram kernel, the next pass's rows by each pass), so stale contents of an earlier call are harmless - but two
 // calls that OVERLAP on one GPU (different streams) race on it.
 constexpr long long RS_STATIC_MAX_ITEMS = 1ll << 22;  // pairs per call
-constexpr size_t RS_STATIC_TILES = (size_t)(RS_STATIC_MAX_ITEMS / (RS_THREADS * 6) + 2);  // 64-bit keys: smallest tiles
-constexpr size_t RS_STATIC_WORDS = (8 * 256 + 64) + 2 * RS_STATIC_TILES * 256;
+constexpr size_t RS_STATIC_WORDS = (8 * 256 + 64) + 2 * (size_t)rs_status_words(scratch_rows(RS_STATIC_MAX_ITEMS));
 static __device__ __align__(256) uint32_t g_rs_static_scratch[RS_STATIC_WORDS];
 
 long long radix_sort_static_max_items() { return RS_STATIC_MAX_ITEMS; }
@@ -696,7 +990,7 @@ int radix_sort_pairs_static(int key_bits, void* keys, void* keys_tmp, uint32_t* 
     const int kb = key_bits / 8;
     SortScratch ss;
     sort_scratch_carve(&ss, base, RS_STATIC_MAX_ITEMS, kb);
-    if ((size_t)((ss.status[1] + (size_t)ss.max_tiles * 256) - base) > RS_STATIC_WORDS) { *err = "static scratch too small (internal)"; return -2; }
+    if ((size_t)((ss.status[1] + (size_t)rs_status_words(ss.max_tiles)) - base) > RS_STATIC_WORDS) { *err = "static scratch too small (internal)"; return -2; }
     int r;
     if (kb == 4)
         r = radix_sort_pairs<uint32_t>((uint32_t*)keys, (uint32_t*)keys, (uint32_t*)keys_tmp, vals, vals_tmp, false, n, nullptr, n,

@@ -196,7 +196,7 @@ int gsr_sort_pairs(gsr_t* h, int key_bits, void* keys, void* keys_tmp, uint32_t*
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
  * it).  Same arguments and result as gsr_sort_pairs minus the handle (it works on the CURRENT device; vals must not be
  * NULL); the scratch of the radix passes (digit histograms, tile tickets, look-back rows) is a static device array
- * inside libgsr.so, about 5.6 MB held by every GPU that loads the library until the process exits.
+ * inside libgsr.so, about 5.8 MB held by every GPU that loads the library until the process exits.
  * Limit: n <= GSR_SORT_STATIC_MAX_PAIRS, larger calls return GSR_EINVAL with a message.  The call makes no cudaMalloc /
  * cudaFree (nor any allocating library call).  Every call on a device shares the one array, which keeps the last call's
  * contents; the sort itself clears what must start at zero, but two calls that OVERLAP on the same GPU (different
@@ -216,30 +216,17 @@ int gsr_alloc_gaussians(gsr_t* h, long long n, int sh_dim);
 /* number of kernels launched by this handle since creation (bench.py's gpu_launches) */
 long long gsr_launch_count(gsr_t* h);
 
-/* ---- measurement (bench.py) ---------------------------------------------------------------------- */
-/* micro-benchmarks for the blend kernel's roofline denominators: FP32 FMA TFLOP/s, 1e12 ex2/s, and a
- * device copy GB/s (read + write).  Synchronises. */
-int gsr_measure_peaks(gsr_t* h, float* fp32_tflops, float* ex2_tops, float* copy_gbs);
-/* re-blends the last frame with counters: (pixel, splat) pairs visited before the pixel terminated, and
- * pairs that contributed a fragment.  Synchronises; the frame buffer passed to the last draw is untouched. */
-int gsr_count_pairs(gsr_t* h, unsigned long long* visited, unsigned long long* contributed);
-
-/* Kernel-variant knobs for measurement runs (process-wide unless noted; images are identical for every setting).
- * GSR_TUNE_BLEND_PPT: pixels per thread of the blend kernel, 1, 2 or 4; 0 (default) = 2 on 16x16 tiles, 4 on 32x32.
- * GSR_TUNE_SORT_SMALL_TILES: 1 = radix passes use 2048-item tiles at 5 CTAs/SM instead of 4096 at 3. */
-#define GSR_TUNE_BLEND_PPT 0
-#define GSR_TUNE_SORT_SMALL_TILES 1
-#define GSR_TUNE_BLEND_SHAPE8 2 /* 1 = a warp owns an 8-column block instead of 16 columns (main mode only) */
-#define GSR_TUNE_SORT_PREFETCH 4 /* 1 (default) = 32-bit-key radix passes use super-tiles: two 4096-key sub-tiles per look-back */
-#define GSR_TUNE_SORT_MATCH_MIX 5 /* 1 = radix ranking sends every other item through MATCH.ANY (ADU pipe) instead of ballots; default 0 (slower) */
+/* Per-handle variant knobs (measurement and cross-checks; images are identical for every setting).  Keys of round 1
+ * that selected kernel variants which no longer exist (0-5, 8) are rejected with GSR_EINVAL. */
 #define GSR_TUNE_FRAME_FORK 6 /* 1 (default) = scratch clears and the tile scan run on an auxiliary stream beside preprocess / depth sort */
-#define GSR_TUNE_TILE 7 /* per handle: tile edge of the shader path in pixels, 32 (default) or 16; images are identical, the instance list, ranges and tiles_x/tiles_y of gsr_stats follow it (GSR_FLAG_OFFICIAL frames always use 16) */
-#define GSR_TUNE_SORT_BALANCE 8 /* 1 (default) = radix passes cut the keys into equal spans, one or more per resident CTA; 0 = fixed 8192-key super-tiles */
-#define GSR_TUNE_FUSED_DEPTH_HIST 9 /* 1 (default) = the preprocess kernel counts the digits of the depth keys (no histogram kernel in the depth sort) */
+#define GSR_TUNE_TILE 7 /* tile edge of the shader path in pixels, 32 (default) or 16; the instance list, ranges and tiles_x/tiles_y of gsr_stats follow it (GSR_FLAG_OFFICIAL frames always use 16) */
+#define GSR_TUNE_FUSED_DEPTH_HIST 9 /* 1 (default) = fast depth sort: the preprocess kernel counts the digits of the rebased depth keys, three compacting 9-bit radix passes over the visible Gaussians; 0 = histogram kernel + four 8-bit passes over all N */
 #define GSR_TUNE_PDL 10 /* bit mask of the kernels launched with programmatic dependent launch (resident behind their predecessor, griddepcontrol.wait before the first memory access): 1 radix passes, 2 duplicate, 4 blend, 8 preprocess; default 11, 0 = plain launches */
 #define GSR_TUNE_FUSED_RGB8 11 /* 1 (default) = gsr_render_rgb8_host_async lets the blend kernel write the RGB8 frame (no k_pack_rgb8 launch) */
-#define GSR_TUNE_BLEND_SKIP 3   /* 0 = none, 1 = warp vote per splat, 2 = warp filter per batch (quad vs the warp's pixel block), 3 (default) = 2 + alpha >= 1/255 reachable in the block */
 int gsr_tune(gsr_t* h, int key, int value);
+
+/* The measurement entry points bench.py uses for its roofline denominators (gsr_measure_peaks, gsr_count_pairs) are
+ * declared in include/gsr_measure.h: they are not part of what a maintainer binds. */
 
 #ifdef __cplusplus
 }

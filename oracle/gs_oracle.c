@@ -24,7 +24,7 @@
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
-#include "../include/gs_tilecull.h"
+#include "gs_tilecull.h"
 #ifdef _OPENMP
 #include <omp.h>
 #endif
@@ -380,7 +380,7 @@ long long gso_tile_instances(const GsoSetup* setup, const GsoVsOut* vs, int cull
         if (!setup[g].ok) continue;
         const int tx0 = setup[g].imin / tile, tx1 = setup[g].imax / tile;
         const int ty0 = setup[g].jmin / tile, ty1 = setup[g].jmax / tile;
-        /* include/gs_tilecull.h: drop tiles in which no pixel can reach alpha >= 1/255 */
+        /* oracle/gs_tilecull.h: drop tiles in which no pixel can reach alpha >= 1/255 */
         const int test = cull && vs && ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= GS_CULL_MAX_TILES);
         const float thr = test ? gs_cull_threshold(vs[g].alpha) : 0.f;
         for (int ty = ty0; ty <= ty1; ++ty)

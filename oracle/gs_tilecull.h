@@ -1,4 +1,7 @@
-/* gs_tilecull.h — the tile-instance rule shared VERBATIM by the CUDA kernels and the CPU oracle.
+/* gs_tilecull.h — TEST INFRASTRUCTURE (oracle/): a tile-exact footprint rule that was costed for the product
+ * (lever 3) and is NOT used by any CUDA kernel; only oracle/gs_oracle.c includes it, to count what
+ * the rule would save.  Original header text follows.
+ * The tile-instance rule, written so that CUDA kernels and the CPU oracle could share it VERBATIM.
  *
  * A Gaussian whose pixel rectangle overlaps a 16x16 tile gets an instance in that tile's list unless
  * no pixel of the tile can pass the fragment shader's `opacity * exp(power) >= 1/255` test
@@ -14,7 +17,7 @@
  * rule conservative against (a) the approximation error of gs_ln_upper, (b) rounding of q, (c) the
  * approximate exp of the blend kernel.
  *
- * Test infrastructure and product both include this header; it contains no reference code.
+ * Only the oracle includes this header today; it contains no reference code.
  */
 #ifndef GS_TILECULL_H
 #define GS_TILECULL_H

@@ -145,7 +145,7 @@ def visible_order(setup):
 
 
 def tile_instances(setup, W, H, tile=16, vs=None, cull=False):
-    """-> (keys u64 sorted, vals u32, ranges (tiles, 2) int32).  cull: apply the include/gs_tilecull.h rule
+    """-> (keys u64 sorted, vals u32, ranges (tiles, 2) int32).  cull: apply the oracle/gs_tilecull.h rule
     (needs the vertex-stage outputs `vs`)."""
     L = oracle_lib()
     n = len(setup)

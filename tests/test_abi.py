@@ -1,4 +1,4 @@
-"""The C-ABI library loads on a CPU-only box and exports every symbol include/gsr.h declares
+"""The C-ABI library loads on a CPU-only box and exports every symbol include/*.h declares
 (no compute calls here); the product path fails loudly without a GPU instead of falling back."""
 import ctypes
 import os
@@ -11,7 +11,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def _declared():
-    src = open(os.path.join(ROOT, "include", "gsr.h")).read()
+    src = "".join(open(os.path.join(ROOT, "include", f)).read() for f in sorted(os.listdir(os.path.join(ROOT, "include")))
+                  if f.endswith(".h"))  # gsr.h (the boundary) + gsr_measure.h (bench.py only)
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(gsr_[a-z0-9_]+)\s*\(", src)))
 

@@ -491,28 +491,26 @@ def test_tile_edge_16_and_32_give_identical_images(R, mod, sm):
     assert np.array_equal(_bits(imgs[0]), _bits(imgs[1]))
 
 
-def test_sort_balance_and_fused_histogram_knobs_change_nothing(R):
-    """The equal-span radix passes and the depth-digit histogram kept by the preprocess kernel are
-    performance variants: instance list, ranges and image are bit-identical to the fixed-tile passes
-    with the sort's own histogram kernel (ragged N: last span partial, culled keys in every pass)."""
-    g = _awkward_scene(300_007, seed=31)
-    W, H = 1280, 720
-    out = []
-    for balance, fused in [(1, 1), (0, 0), (0, 1), (1, 0)]:
-        r, _ = _setup(R, g, W, H, debug=False)
-        r.tune(_gsr.GSR_TUNE_SORT_BALANCE, balance)
-        r.tune(_gsr.GSR_TUNE_FUSED_DEPTH_HIST, fused)
-        try:
+def test_fast_and_generic_depth_sort_agree_bitwise(R):
+    """The frame's fast depth sort (digit counts from the preprocess kernel, a compacting first pass, three 9-bit
+    passes over the rebased keys of the visible Gaussians) against the generic one (histogram kernel, four 8-bit
+    passes over all N keys with the culled ones at the end): instance list, ranges and image bit-identical
+    (ragged N: last span partial; a scene where most Gaussians are culled; per-handle knob)."""
+    for n, eye in [(300_007, (0.0, 0.0, 10.0)), (200_003, (0.0, 0.0, 2.5)), (5_001, (3.0, 1.0, 6.0))]:
+        g = _awkward_scene(n, seed=31)
+        W, H = 1280, 720
+        out = []
+        for fast in (1, 0):
+            r, _ = _setup(R, g, W, H, eye=eye, debug=False)
+            r.tune(_gsr.GSR_TUNE_FUSED_DEPTH_HIST, fast)
             img = r.draw().cpu().numpy()
             out.append((_bits(img), r.debug_fetch(_gsr.GSR_DBG_INST_VALS, np.uint32),
                         r.debug_fetch(_gsr.GSR_DBG_RANGES, np.int32)))
-        finally:
-            r.tune(_gsr.GSR_TUNE_SORT_BALANCE, 1)
-            r.tune(_gsr.GSR_TUNE_FUSED_DEPTH_HIST, 1)
-    for o in out[1:]:
-        for a, b in zip(out[0], o):
-            assert np.array_equal(a, b)
-    assert len(out[0][1]) > 0
+            r2, _ = _setup(R, g, W, H, eye=eye, debug=False)   # another handle keeps its own (default) setting
+            assert np.array_equal(_bits(r2.draw().cpu().numpy()), out[0][0])
+        for a_, b_ in zip(out[0], out[1]):
+            assert np.array_equal(a_, b_)
+        assert len(out[0][1]) > 0
 
 
 @pytest.mark.parametrize("W,H,tile", [(483, 271, 32), (484, 270, 16), (96, 64, 32), (50, 30, 32)])
