@@ -141,6 +141,8 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    from gaussiansplattingviewer_b200 import pose_shard as _ps
+    numa_cpus = _ps.bind_to_gpu_numa_node(local) if world > 1 else None  # pinned read-back buffers on the GPU's own node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     wl = WORKLOADS[args.workload]
@@ -252,7 +254,7 @@ def run_ours(args):
         out["pairs"] = r.count_pairs()
         r.tune(_gsr.GSR_TUNE_TILE, 32)
         out["peaks"] = r.measure_peaks()
-    out.update(rank=rank, world=world, W=W, H=H, n=n, mod=mod, K=K, Wm=Wm, renderer=r, scene=g if rank == 0 else None,
+    out.update(numa=numa_cpus, rank=rank, world=world, W=W, H=H, n=n, mod=mod, K=K, Wm=Wm, renderer=r, scene=g if rank == 0 else None,
                cam=cam, pose=pose_of(Wm + K - 1))
     if world > 1:
         dist.barrier()
@@ -272,7 +274,9 @@ def run_config5(r, cam, rank, world, sync_all, W, H, n_poses=1024):
     from gaussiansplattingviewer_b200 import pose_shard, scenes
     rows = np.load(os.path.join(ROOT, "tests", "golden", "camera_data.npy"))
     views, campos = scenes.trajectory_poses(rows, n_poses)
-    lo, hi = pose_shard.shard_range(n_poses, rank, world)
+    # interleaved assignment (pose_shard.shard_round_robin): the cost of a pose varies along the trajectory, contiguous
+    # slices left one rank 14 % longer than the other at N = 2 (219 vs 250 ms)
+    mine = pose_shard.shard_round_robin(n_poses, rank, world)
     zero3 = np.zeros(3, np.float32)
 
     def pose(i):
@@ -280,7 +284,7 @@ def run_config5(r, cam, rank, world, sync_all, W, H, n_poses=1024):
 
     res = {}
     for name in ("device", "e2e"):
-        for i in range(lo, min(lo + 3, hi)):  # warm-up on the slice's first poses
+        for i in mine[:3]:  # warm-up on the rank's first poses
             r.update_camera_pose(cam, True, pose(i))
             r.draw() if name == "device" else r.read_pixels_rgb8_async()
         r.sync_host()
@@ -288,9 +292,11 @@ def run_config5(r, cam, rank, world, sync_all, W, H, n_poses=1024):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record()
-        for i in range(lo, hi):
+        t_enq0 = time.perf_counter()
+        for i in mine:
             r.update_camera_pose(cam, True, pose(i))
             r.draw() if name == "device" else r.read_pixels_rgb8_async()
+        enqueue_us = (time.perf_counter() - t_enq0) * 1e6 / max(len(mine), 1)  # host time per pose inside the loop
         if name == "e2e":
             r.sync_host()
         e1.record()
@@ -309,12 +315,11 @@ def run_config5(r, cam, rank, world, sync_all, W, H, n_poses=1024):
         res[name] = {"views_per_s": round(n_poses / (max(per_rank) * 1e-3), 1), "ms_total_max_over_ranks": round(max(per_rank), 3),
                      "per_rank_ms": {"min": round(min(per_rank), 3), "median": round(float(np.median(per_rank)), 3),
                                      "max": round(max(per_rank), 3)},
-                     "poses_per_rank": [pose_shard.shard_range(n_poses, k, world)[1] - pose_shard.shard_range(n_poses, k, world)[0]
-                                        for k in range(world)][:2] + (["..."] if world > 2 else []),
-                     "rank0_wall_ms": round(host_ms, 3)}
+                     "poses_rank0": len(mine), "rank0_wall_ms": round(host_ms, 3),
+                     "rank0_host_us_per_pose_in_loop": round(enqueue_us, 1)}
     assert not r.stats().overflow
     return {"workload": "1024 poses (closed Catmull-Rom loop through camera_data.csv, x3 about the origin) over the "
-                        "3M SH3 scene at 1920x1080, contiguous slices per rank (pose_shard.shard_range)",
+                        "3M SH3 scene at 1920x1080, poses dealt round-robin to the ranks (pose_shard.shard_round_robin)",
             "n_poses": n_poses, "scaling": "strong", "views_per_s": res["device"]["views_per_s"],
             "views_per_s_e2e": res["e2e"]["views_per_s"], "device": res["device"], "e2e": res["e2e"],
             "d2h_bytes_per_view": W * H * 3}
@@ -605,6 +610,7 @@ def main():
             "peaks": {"hbm_gbs": hbm_peak, "hbm_source": peak_src, "fp32_tflops": round(fp32_peak, 2),
                       "ex2_tops": round(ex2_peak, 3), "copy_gbs_this_run": round(copy_gbs, 1)},
             "scene_broadcast_ms": round(o["t_bcast_ms"], 3)}
+    line["host"] = {"cpu_affinity_cores": len(os.sched_getaffinity(0)), "bound_to_gpu_numa_node": o.get("numa") is not None}
     # BASELINE.json's metric also names "sort Gkeys/s": the two sorts inside the frame (keys through a complete
     # key/value sort per second: 32 depth bits over N, the tile bits over D) and, at N=1, the standalone
     # gsr_sort_pairs on 2^24 random 32-bit keys with 32-bit values (all 32 bits, CUDA events, best of 5)

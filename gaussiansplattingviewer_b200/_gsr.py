@@ -26,6 +26,7 @@ GSR_TUNE_TILE = 7
 GSR_TUNE_FUSED_DEPTH_HIST = 9
 GSR_TUNE_PDL = 10
 GSR_TUNE_FUSED_RGB8 = 11
+GSR_TUNE_GRAPH = 12
 
 
 class Stats(C.Structure):

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "../../include/gsr.h"
 #include "../../include/gsr_measure.h"
@@ -34,6 +35,8 @@ int fail(int code, const std::string& msg) {
 
 constexpr long long MAX_CAPACITY = (1ll << 30) - 1;
 
+void drop_graphs(gsr_t* h);  // captured frames refer to buffers: every (re)allocation drops them
+
 template <typename T>
 void dfree(T*& p) {
     if (p) cudaFree(p);
@@ -41,6 +44,25 @@ void dfree(T*& p) {
 }
 
 }  // namespace
+
+// a captured frame (see render_frame)
+struct GraphKey {
+    long long n, capacity; const void *out, *out_rgb8, *dbg;
+    int sh_dim, W, H, tile_req, order_mode, order_buf_in, blend_class, pdl, fused_hist, fork;
+    unsigned flags, epoch;
+};
+struct FrameGraph {
+    GraphKey key;
+    cudaGraphExec_t exec = nullptr;     // nullptr: the key was seen once, not captured yet
+    cudaGraph_t graph = nullptr;        // the captured graph: owns params_node, lives as long as exec
+    cudaGraphNode_t params_node = nullptr;
+    cudaKernelNodeParams params_base = {};
+    long long launches = 0;             // kernels of one frame (gsr_launch_count)
+    int order_buf_after = -1, last_result_buf = 0;
+    bool order_count_dev_after = false, last_keys64 = false;
+    unsigned long long last_use = 0;
+};
+constexpr int MAX_FRAME_GRAPHS = 12;
 
 struct gsr_renderer {
     int device = 0;
@@ -105,6 +127,11 @@ struct gsr_renderer {
     cudaEvent_t ev[8] = {};
     long long launches = 0;
     GsrTune tune;  // gsr_tune state (per handle)
+    // captured frames (render_frame)
+    std::vector<FrameGraph> graphs;
+    unsigned graph_epoch = 0;
+    unsigned long long graph_clock = 0;
+    cudaStream_t cap_stream = nullptr;
     // scratch for gsr_sort_pairs
     void* d_sortp = nullptr;
     long long sortp_items = 0;
@@ -117,6 +144,7 @@ namespace {
 
 
 int free_gaussian_buffers(gsr_t* h) {
+    drop_graphs(h);
     dfree(h->d_xyz); dfree(h->d_rot); dfree(h->d_scale_op); dfree(h->d_sh);
     dfree(h->sp.rec0); dfree(h->sp.rec1); dfree(h->sp.rec2); dfree(h->sp.depth_key); dfree(h->sp.trect);
     dfree(h->sp.dbg_vsout); dfree(h->sp.dbg_setup);
@@ -127,6 +155,7 @@ int free_gaussian_buffers(gsr_t* h) {
 }
 
 int free_instance_buffers(gsr_t* h) {
+    drop_graphs(h);
     dfree(h->d_ikeys[0]); dfree(h->d_ikeys[1]); dfree(h->d_ivals[0]); dfree(h->d_ivals[1]);
     dfree(h->d_sorti); dfree(h->d_dbgkeys);
     h->capacity = 0;
@@ -167,7 +196,9 @@ int ensure_debug_buffers(gsr_t* h) {
     if (h->fp.flags & GSR_FLAG_DEBUG) {
         if (!h->sp.dbg_vsout) CK(cudaMalloc(&h->sp.dbg_vsout, n1 * 16 * sizeof(float)));
         if (!h->sp.dbg_setup) CK(cudaMalloc(&h->sp.dbg_setup, n1 * 8 * sizeof(int)));
-    } else {
+    } else if (h->sp.dbg_vsout || h->sp.dbg_setup) {
+        CK(cudaDeviceSynchronize());  // frames in flight may still write them
+        drop_graphs(h);
         dfree(h->sp.dbg_vsout);
         dfree(h->sp.dbg_setup);
     }
@@ -210,8 +241,19 @@ int tile_bits(int n_tiles) {
 // Enqueues one frame.  timed: record events between stages (h->ev[0..6]).
 // order_mode: 0 = sort this frame's depth keys; 1 = same, with keys for every Gaussian in front of the camera, and
 // remember the order; 2 = reuse the remembered order (same view-space depths: same view up to an in-plane shift)
-int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode = 0,
-                 uint8_t* out_rgb8 = nullptr) {
+// What a frame's kernels are launched with that changes from frame to frame (the uniforms) plus what decides WHICH
+// kernels and buffers a frame uses (the key of a captured graph).
+struct FramePlan {
+    FrameParams fp;         // final uniforms (official matrices, tiling, depth plan)
+    long long n_keys_init;  // k_set_params: counters->n_keys at frame start
+    int* zero_a; long long na; uint32_t* zero_b; int nb;  // k_set_params: the two clears
+    int order_mode;         // after the adjustments of frame_body
+    int blend_class;        // which k_blend instance: 0 gaussian, 2 billboard, 3 flat ball, 4 gaussian ball, 5 official
+    bool fused_hist, fork;
+};
+
+int frame_body(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode,
+               uint8_t* out_rgb8, FramePlan* plan_only) {
     FrameParams fp = fp_in;
     g_pdl = h->tune.pdl;
     if (fp.flags & GSR_FLAG_KEYS64) {
@@ -278,11 +320,6 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     const bool fork = !timed && !keys64 && h->tune.frame_fork;
     cudaStream_t sa = fork ? h->aux_stream : s;
     const long long sort_upper = cap;
-    if (timed) cudaEventRecord(h->ev[0], s);
-    if (fork) {
-        CK(cudaEventRecord(h->ev_start, s));
-        CK(cudaStreamWaitEvent(sa, h->ev_start, 0));
-    }
     // Fast depth sort of the shader path: a visible depth lies in [0.1, 100] (depth clip), so its bits minus those of
     // 0.05 are a 27-bit integer - three 9-bit radix passes.  The preprocess kernel counts those digits while it writes
     // the keys (no histogram kernel), the first pass drops the culled Gaussians (compaction, ties keep ascending
@@ -297,6 +334,22 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     // (generic path), or what the stored order has (reuse)
     long long n_keys_init = fused_hist ? 0 : N;
     if (order_mode == 2) n_keys_init = h->order_count_dev ? -1 : N;
+    if (plan_only) {  // everything above is host work; nothing has been enqueued
+        plan_only->fp = fp;
+        plan_only->n_keys_init = n_keys_init;
+        plan_only->zero_a = h->d_tile_grid; plan_only->na = (long long)sp.grid_stride * GSR_GRID_REPLICAS;
+        plan_only->zero_b = sp.depth_hist; plan_only->nb = sp.depth_hist ? 3 * 512 : 0;
+        plan_only->order_mode = order_mode;
+        plan_only->blend_class = official ? 5 : (fp.render_mod == -2 ? 2 : (fp.render_mod == -3 ? 3 : (fp.render_mod == -4 ? 4 : 0)));
+        plan_only->fused_hist = fused_hist;
+        plan_only->fork = fork;
+        return 0;
+    }
+    if (timed) cudaEventRecord(h->ev[0], s);
+    if (fork) {
+        CK(cudaEventRecord(h->ev_start, s));
+        CK(cudaStreamWaitEvent(sa, h->ev_start, 0));
+    }
     // uniforms, counters, and the clears of the corner-impulse grid and of those histograms in one launch
     launch_set_params(h->d_fp, fp, h->d_counters, s, h->d_tile_grid, (long long)sp.grid_stride * GSR_GRID_REPLICAS,
                       sp.depth_hist, 3 * 512, n_keys_init);
@@ -404,6 +457,103 @@ int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s,
     return 0;
 }
 
+// ---- the frame as a CUDA graph ---------------------------------------------------------------------------------
+// A frame is 12 kernels, a few memsets and a small copy, forked over two streams: enqueued one by one that is ~20
+// driver calls per frame.  Frames of one configuration differ only in the uniforms, which live in device memory and
+// are written by the frame's first kernel (k_set_params) - so the stream operations of a configuration are captured
+// once and replayed with that kernel node's arguments updated (FramePlan).  What selects kernels or buffers is the key.
+void drop_graphs(gsr_t* h) {
+    for (FrameGraph& g : h->graphs) {
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+        if (g.graph) cudaGraphDestroy(g.graph);
+    }
+    h->graphs.clear();
+    ++h->graph_epoch;
+}
+
+int render_frame(gsr_t* h, const FrameParams& fp_in, float* out, cudaStream_t s, bool timed, int order_mode = 0,
+                 uint8_t* out_rgb8 = nullptr) {
+    if (timed || !h->tune.graph) return frame_body(h, fp_in, out, s, timed, order_mode, out_rgb8, nullptr);
+    FramePlan plan;
+    int rc = frame_body(h, fp_in, out, s, false, order_mode, out_rgb8, &plan);  // validates, (re)allocates, plans
+    if (rc) return rc;
+    GraphKey key;
+    memset(&key, 0, sizeof(key));
+    key.n = h->N; key.capacity = h->capacity; key.out = out; key.out_rgb8 = out_rgb8; key.dbg = h->sp.dbg_vsout;
+    key.sh_dim = h->sh_dim; key.W = h->W; key.H = h->H; key.tile_req = h->tile_req; key.order_mode = plan.order_mode;
+    key.order_buf_in = (plan.order_mode == 2) ? h->order_buf : -1;
+    key.blend_class = plan.blend_class; key.pdl = h->tune.pdl; key.fused_hist = plan.fused_hist; key.fork = plan.fork;
+    key.flags = plan.fp.flags; key.epoch = h->graph_epoch;
+    FrameGraph* g = nullptr;
+    for (FrameGraph& e : h->graphs) if (memcmp(&e.key, &key, sizeof(key)) == 0) { g = &e; break; }
+    if (!g) {  // first frame of this configuration: enqueue directly (lazy one-time set-up happens here), remember the key
+        if ((int)h->graphs.size() >= MAX_FRAME_GRAPHS) {
+            size_t victim = 0;
+            for (size_t i = 1; i < h->graphs.size(); ++i) if (h->graphs[i].last_use < h->graphs[victim].last_use) victim = i;
+            if (h->graphs[victim].exec) cudaGraphExecDestroy(h->graphs[victim].exec);
+            if (h->graphs[victim].graph) cudaGraphDestroy(h->graphs[victim].graph);
+            h->graphs.erase(h->graphs.begin() + victim);
+        }
+        FrameGraph e;
+        e.key = key;
+        e.last_use = ++h->graph_clock;
+        h->graphs.push_back(e);
+        return frame_body(h, fp_in, out, s, false, order_mode, out_rgb8, nullptr);
+    }
+    g->last_use = ++h->graph_clock;
+    bool fresh = false;
+    if (!g->exec) {  // second frame: capture
+        const long long l0 = h->launches;
+        cudaGraph_t graph = nullptr;
+        cudaError_t e = cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal);
+        if (e == cudaSuccess) {
+            rc = frame_body(h, fp_in, out, h->cap_stream, false, order_mode, out_rgb8, nullptr);
+            e = cudaStreamEndCapture(h->cap_stream, &graph);
+            if (rc != 0 && e == cudaSuccess) e = cudaErrorUnknown;
+        }
+        if (e == cudaSuccess) e = cudaGraphInstantiate(&g->exec, graph, 0);
+        if (e == cudaSuccess) {  // find the k_set_params node
+            size_t nn = 0;
+            cudaGraphGetNodes(graph, nullptr, &nn);
+            std::vector<cudaGraphNode_t> nodes(nn);
+            cudaGraphGetNodes(graph, nodes.data(), &nn);
+            for (cudaGraphNode_t nd : nodes) {
+                cudaGraphNodeType ty;
+                if (cudaGraphNodeGetType(nd, &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+                cudaKernelNodeParams kp = {};
+                if (cudaGraphKernelNodeGetParams(nd, &kp) == cudaSuccess && kp.func == set_params_kernel()) {
+                    g->params_node = nd; g->params_base = kp; break;
+                }
+            }
+            if (!g->params_node) e = cudaErrorUnknown;
+        }
+        if (e != cudaSuccess) {  // this driver / configuration cannot be captured: frames are enqueued directly from now on
+            cudaGetLastError();
+            if (g->exec) { cudaGraphExecDestroy(g->exec); g->exec = nullptr; }
+            if (graph) cudaGraphDestroy(graph);
+            h->tune.graph = 0;
+            h->launches = l0;
+            return frame_body(h, fp_in, out, s, false, order_mode, out_rgb8, nullptr);
+        }
+        g->graph = graph;
+        g->launches = h->launches - l0;
+        g->order_buf_after = h->order_buf; g->order_count_dev_after = h->order_count_dev;
+        g->last_result_buf = h->last_result_buf; g->last_keys64 = h->last_keys64;
+        fresh = true;
+    }
+    // replay with this frame's uniforms
+    if (set_params_node_update(g->exec, g->params_node, g->params_base, h->d_fp, plan.fp, h->d_counters, plan.zero_a, plan.na,
+                               plan.zero_b, plan.nb, plan.n_keys_init) != 0)
+        return fail(GSR_ECUDA, std::string("graph parameter update failed: ") + cudaGetErrorString(cudaGetLastError()));
+    CK(cudaGraphLaunch(g->exec, s));
+    if (!fresh) h->launches += g->launches;
+    if (plan.order_mode != 2) { h->order_buf = g->order_buf_after; h->order_count_dev = g->order_count_dev_after; }
+    h->last_result_buf = g->last_result_buf;
+    h->last_keys64 = g->last_keys64;
+    h->frame_valid = true;
+    return 0;
+}
+
 // The asynchronous entry points (gsr_render, gsr_render_batch) cannot know whether the frame they enqueue fits the
 // instance buffers; k_tile_scan counts such frames in the sticky words, whose pinned copy the NEXT call looks at:
 // it grows the buffers and tells the caller (GSR_EOVERFLOW) that an earlier frame was incomplete.
@@ -494,6 +644,7 @@ int gsr_create(int device, gsr_t** out) {
     for (auto& ev : h->ev) CK(cudaEventCreate(&ev));
     CK(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
     for (cudaEvent_t* e : {&h->ev_start, &h->ev_pre, &h->ev_cleared, &h->ev_scan})
         CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     for (int i = 0; i < 2; ++i) {
@@ -517,6 +668,8 @@ int gsr_destroy(gsr_t* h) {
     dfree(h->d_cap[0]); dfree(h->d_cap[1]);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->aux_stream) cudaStreamDestroy(h->aux_stream);
+    drop_graphs(h);
+    if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
     for (cudaEvent_t e : {h->ev_start, h->ev_pre, h->ev_cleared, h->ev_scan}) if (e) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) { if (h->ev_packed[i]) cudaEventDestroy(h->ev_packed[i]); if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]); }
     dfree(h->d_fp); dfree(h->d_counters); dfree(h->d_sortp);
@@ -686,6 +839,7 @@ int gsr_set_resolution(gsr_t* h, int width, int height) {
     CK(cudaSetDevice(h->device));
     if (width == h->W && height == h->H) return 0;
     CK(cudaDeviceSynchronize());
+    drop_graphs(h);
     dfree(h->d_ranges); dfree(h->d_tile_grid); dfree(h->d_frame); dfree(h->d_rgb8); dfree(h->d_rgb8b); dfree(h->d_r32);
     dfree(h->d_cap[0]); dfree(h->d_cap[1]);
     h->slot_busy[0] = h->slot_busy[1] = false;
@@ -1121,6 +1275,7 @@ int gsr_tune(gsr_t* h, int key, int value) {
         case GSR_TUNE_PDL: h->tune.pdl = value; return 0;
         case GSR_TUNE_FUSED_RGB8: h->tune.fused_rgb8 = value ? 1 : 0; return 0;
         case GSR_TUNE_FRAME_FORK: h->tune.frame_fork = value ? 1 : 0; return 0;
+        case GSR_TUNE_GRAPH: h->tune.graph = value ? 1 : 0; return 0;
         case GSR_TUNE_TILE:
             if (value != 16 && value != 32) return fail(GSR_EINVAL, "tile edge must be 16 or 32");
             h->tile_req = value;

@@ -82,6 +82,7 @@ struct GsrTune {
     int fast_depth_sort = 1;   // GSR_TUNE_FUSED_DEPTH_HIST: digit counts from the preprocess kernel + compacting 9-bit passes
     int fused_rgb8 = 1;        // GSR_TUNE_FUSED_RGB8
     int frame_fork = 1;        // GSR_TUNE_FRAME_FORK
+    int graph = 1;             // GSR_TUNE_GRAPH: frames of a configuration are replayed from a captured CUDA graph
 };
 extern thread_local int g_pdl;  // PDL mask of the handle whose frame is being enqueued on this thread
 #ifdef __CUDACC__
@@ -182,6 +183,11 @@ void launch_keys64_from_ranges(const int2* ranges, int n_tiles, const uint32_t* 
 void launch_blend_count(const FrameParams* fp, const int2* ranges, const uint32_t* inst_gid, SplatBuffers sp,
                         float* out_rgba, int render_mod, unsigned flags, int tiles_x, int tiles_y,
                         unsigned long long* pair_counts, cudaStream_t s, int tile = 16);
+// the k_set_params kernel (to find its node in a captured frame) and the update of that node's arguments
+const void* set_params_kernel();
+int set_params_node_update(cudaGraphExec_t exec, cudaGraphNode_t node, const cudaKernelNodeParams& base, FrameParams* dst,
+                           const FrameParams& fp, FrameCounters* counters, int* zero_a, long long na, uint32_t* zero_b, int nb,
+                           long long n_keys_init);
 int preprocess_prepare_device();  // per-device kernel opt-ins (gsr_create)
 int sm_count_current();           // SM count of the current device (cached per device)
 int measure_peaks_impl(float* fp32_tflops, float* ex2_tops, float* copy_gbs);

@@ -704,6 +704,21 @@ void launch_set_params(FrameParams* dst, const FrameParams& fp, FrameCounters* c
     k_set_params<<<(unsigned)grid, 256, 0, s>>>(dst, fp, counters, zero_a, zero_a ? na : 0, zero_b, zero_b ? nb : 0, n_keys_init);
 }
 
+const void* set_params_kernel() { return (const void*)k_set_params; }
+
+int set_params_node_update(cudaGraphExec_t exec, cudaGraphNode_t node, const cudaKernelNodeParams& base, FrameParams* dst,
+                           const FrameParams& fp_in, FrameCounters* counters, int* zero_a, long long na, uint32_t* zero_b, int nb,
+                           long long n_keys_init) {
+    FrameParams fp = fp_in;
+    if (!zero_a) na = 0;
+    if (!zero_b) nb = 0;
+    void* args[8] = {&dst, &fp, &counters, &zero_a, &na, &zero_b, &nb, &n_keys_init};  // k_set_params' parameter list
+    cudaKernelNodeParams p = base;
+    p.kernelParams = args;
+    p.extra = nullptr;
+    return cudaGraphExecKernelNodeSetParams(exec, node, &p) == cudaSuccess ? 0 : -1;
+}
+
 int sm_count_current() {
     static int cache[64] = {};
     int dev = 0;

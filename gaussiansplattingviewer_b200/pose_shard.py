@@ -26,6 +26,35 @@ def shard_round_robin(n_items: int, rank: int, world: int):
     return list(range(rank, n_items, world))
 
 
+def bind_to_gpu_numa_node(device_index: int):
+    """Pins the calling process to the CPU cores that are local to the GPU's PCIe root (sysfs `local_cpulist`), BEFORE
+    it allocates pinned host buffers: the read-back copies then land in memory of the GPU's own NUMA node.  torchrun
+    does not do this.  Returns the core list, or None when sysfs does not tell (then nothing is changed)."""
+    import os
+    import torch
+    try:
+        bus = torch.cuda.get_device_properties(device_index).pci_bus_id
+        dom = torch.cuda.get_device_properties(device_index).pci_domain_id
+        dev = torch.cuda.get_device_properties(device_index).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/local_cpulist"
+        with open(path) as f:
+            spec = f.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return sorted(cpus)
+    except Exception:
+        return None
+
+
 def broadcast_scene(gaus, device, src: int = 0):
     """Replicates a scene from rank `src` to every rank.  `gaus` is a GaussianData on the source rank
     (ignored elsewhere).  Returns the five arrays as torch tensors on `device`, in GaussianData order."""

@@ -223,6 +223,7 @@ long long gsr_launch_count(gsr_t* h);
 #define GSR_TUNE_FUSED_DEPTH_HIST 9 /* 1 (default) = fast depth sort: the preprocess kernel counts the digits of the rebased depth keys, three compacting 9-bit radix passes over the visible Gaussians; 0 = histogram kernel + four 8-bit passes over all N */
 #define GSR_TUNE_PDL 10 /* bit mask of the kernels launched with programmatic dependent launch (resident behind their predecessor, griddepcontrol.wait before the first memory access): 1 radix passes, 2 duplicate, 4 blend, 8 preprocess; default 11, 0 = plain launches */
 #define GSR_TUNE_FUSED_RGB8 11 /* 1 (default) = gsr_render_rgb8_host_async lets the blend kernel write the RGB8 frame (no k_pack_rgb8 launch) */
+#define GSR_TUNE_GRAPH 12 /* 1 (default) = the stream operations of a frame configuration are captured once as a CUDA graph and replayed with new uniforms; 0 = every frame is enqueued kernel by kernel */
 int gsr_tune(gsr_t* h, int key, int value);
 
 /* The measurement entry points bench.py uses for its roofline denominators (gsr_measure_peaks, gsr_count_pairs) are
