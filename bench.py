@@ -325,6 +325,53 @@ def run_config5(r, cam, rank, world, sync_all, W, H, n_poses=1024):
             "d2h_bytes_per_view": W * H * 3}
 
 
+def run_stereo(r, cam, n_poses=40):
+    """The viewer's stereo capture loop (/root/reference/main.py:844-917, one scene of render_all.py:14-35): per pose left
+    RGB8 + disparity uint16 (render_mod -1 at the left pose) + right RGB8 into pinned host buffers.  poses/s through
+    B200Renderer.capture_stereo (one depth order per pose shared by the three renders, copies overlapped with the next
+    pose) next to a straight port of the reference loop (three synchronous read-backs per pose)."""
+    import torch
+    from gaussiansplattingviewer_b200 import colmap, scenes
+    views, campos = scenes.orbit_poses(n_poses)
+    front, up = np.array([0, 0, 1], np.float32), np.array([0, -1, 0], np.float32)
+    poses = []
+    for v, c in zip(views, campos):
+        vr = colmap.right_view(v)
+        poses.append(({"camera_view": v, "camera_position": c, "camera_front": front, "camera_up": up},
+                      {"camera_view": vr, "camera_position": colmap.camera_position_of(vr), "camera_front": front, "camera_up": up}))
+    r.set_render_mod(3)
+
+    def capture(share):
+        for pl, pr in poses[:3]:
+            r.capture_stereo(pl, pr, share_order=share)
+        r.sync_host(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for pl, pr in poses:
+            r.capture_stereo(pl, pr, share_order=share)
+        r.sync_host(); torch.cuda.synchronize()
+        return len(poses) / (time.perf_counter() - t0)
+
+    def port():
+        def one(pl, pr):
+            r.set_render_mod(3); r.update_camera_pose(cam, True, pl); r.read_pixels_rgb8()
+            r.set_render_mod(-1); r.read_pixels_r32f()
+            r.set_render_mod(3); r.update_camera_pose(cam, True, pr); r.read_pixels_rgb8()
+        for pl, pr in poses[:2]:
+            one(pl, pr)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for pl, pr in poses[:20]:
+            one(pl, pr)
+        torch.cuda.synchronize()
+        r.set_render_mod(3)
+        return 20 / (time.perf_counter() - t0)
+
+    out = {"poses_per_s_shared_order": round(capture(True), 1), "poses_per_s_three_sorts": round(capture(False), 1),
+           "poses_per_s_three_synchronous_readbacks": round(port(), 1), "poses": n_poses,
+           "d2h_bytes_per_pose": r.w * r.h * 8, "api": "B200Renderer.capture_stereo (gsr_capture_stereo_async)"}
+    return out
+
+
 def run_config4(local, K=10):
     """BASELINE.json configs[3]: 6M SH3 Gaussians at 3840x2160, colour (3), depth/disparity (-1, the 1.2x-scale second
     geometry pass, gau_vert.glsl:151-156,182-211) and flat ball (-3).  Frames/s with the scene resident (CUDA events
@@ -635,6 +682,9 @@ def main():
         line["sort"]["pairs_2p24_u32_gkeys_s"] = round(m / (best * 1e-3) / 1e9, 2)
         line["sort"]["pairs_2p24_u32_ms"] = round(best, 4)
         line["sort"].update(sort_baselines(o["renderer"], o["scene"], o["pose"]["camera_view"]))
+        if args.workload == "3M_sh3_1080p":
+            line["stereo"] = run_stereo(o["renderer"], o["cam"])
+            o["renderer"].update_camera_pose(o["cam"], True, o["pose"])  # back to the last timed pose (cpu_baseline below)
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle as O
         img, t_sort, t_rast = cpu_frame(o["scene"], o["cam"], o["pose"], W, H, o["mod"], use_ref=False)

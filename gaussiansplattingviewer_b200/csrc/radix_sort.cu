@@ -131,133 +131,171 @@ __device__ __forceinline__ uint32_t match_digit_t(uint32_t d) {
     return peers;
 }
 
-// ---- inter-tile prefixes of k_rs_pass3: two-level sums behind per-tile flags --------------------------------------
+// ---- inter-tile prefixes of k_rs_pass3: two-level look-back over self-validating words ------------------------------
 // The decoupled look-back of k_rs_pass (every thread walks back over the count rows of its digit until it meets an
 // inclusive prefix) is a poor fit for persistent CTAs that run in lock step: all tiles of a wave finish ranking at about
-// the same time, the front of inclusive prefixes then advances a window per L2 round trip, and all 256 threads of
-// every waiting CTA spin on 16 volatile loads each, taking issue slots from the CTAs that still rank (ncu: half of the
-// executed instructions and 45 % of the stall samples of a pass were that loop; switching it off - wrong result, timing
-// only - took 13 to 18 us off a 45 us pass).  Here nothing is chained:
-//   * a tile publishes its count row (AGG) and then ONE flag word;
-//   * tiles form groups of RS_GROUP; the tile that completes a group (atomic arrival counter) sums the group's rows
-//     into a GROUP row behind a group flag;
-//   * the first tile of a group publishes the exclusive prefix at the start of the group (a checkpoint) once it has it;
-//   * a tile's prefix = nearest checkpoint + GROUP rows since + the rows of the tiles in front of it in its own group:
-//     at most (tiles in flight) / RS_GROUP + RS_GROUP rows, all loads independent.
-// Waiting is done by warp 0 alone (one coalesced load of flag words per poll, with a back-off) while the other warps sit
-// at the barrier.  Every wait is for a tile with a smaller ticket, so forward progress needs what the look-back needed.
-// One status buffer: [flag words: tile_flag[R] | group_cnt[G] | group_flag[G] | ckpt_flag[G]] [AGG R rows] [GROUP G rows]
-// [CKPT G rows], R = rows, G = R / RS_GROUP + 1, rows of `stride` words.  Only the flag words have to start at zero.
+// the same time, nothing in front of them has an inclusive prefix yet, and every thread walks back over hundreds of rows,
+// 16 volatile loads per round trip, while it takes issue slots from the CTAs that still rank (ncu: half of the executed
+// instructions and 45 % of the stall samples of a pass were that loop).  Here the walk is over GROUPS of RS_GROUP tiles:
+//   AGG[tile][d]   = count of digit d in the tile                      (published by the tile, first thing)
+//   GROUP[g][d]    = sum of AGG over the tiles of group g              (published by the LAST tile of the group, as soon
+//                                                                       as the 15 rows in front of it are there)
+//   CKPT[g][d]     = exclusive prefix at the start of group g          (published by the last tile of group g - 1 once
+//                                                                       it knows its own prefix; CKPT[0] = 0 implicitly)
+//   prefix(tile)   = CKPT[h] + sum GROUP[h .. g-1] + sum AGG of the tiles in front of it in its own group g,
+//                    h = the nearest group at or below g whose checkpoint is there.
+// Every word carries its own ready bit (bit 31) next to a 31-bit value, so a word is complete the moment it is visible:
+// no fences, no barriers, no atomics, every thread follows its own digits.  All loads of a step are issued before the
+// first is consumed; what is not ready is read again after a back-off.  Every wait is for a tile with a smaller ticket.
+// One status buffer: [AGG rows][GROUP rows][CKPT rows], rows of `stride` words, all zero at the start of a pass.
 constexpr int RS_GROUP = 16;
-struct RsStatus {
-    uint32_t* tile_flag; uint32_t* group_cnt; uint32_t* group_flag; uint32_t* ckpt_flag;
-    uint32_t* agg; uint32_t* group; uint32_t* ckpt;
-    long long flag_words;
-};
-__host__ __device__ constexpr long long rs_status_groups(long long rows) { return rows / RS_GROUP + 1; }
-__host__ __device__ constexpr long long rs_status_flag_words(long long rows) { return (rows + 3 * rs_status_groups(rows) + 511) & ~511ll; }
+constexpr uint32_t RS_READY = 0x80000000u;
+struct RsStatus { uint32_t* agg; uint32_t* group; uint32_t* ckpt; long long groups; };
+__host__ __device__ constexpr long long rs_status_groups(long long rows) { return rows / RS_GROUP + 2; }
+__host__ __device__ constexpr long long rs_status_rows_total(long long rows) { return rows + 2 * rs_status_groups(rows); }
 // words of one status buffer with rows of up to 512 words
-__host__ __device__ constexpr long long rs_status_words(long long rows) { return rs_status_flag_words(rows) + (rows + 2 * rs_status_groups(rows)) * 512; }
+__host__ __device__ constexpr long long rs_status_words(long long rows) { return rs_status_rows_total(rows) * 512; }
 __host__ __device__ inline RsStatus rs_status_carve(uint32_t* base, long long rows, int stride) {
     RsStatus st;
-    const long long g = rs_status_groups(rows);
-    st.tile_flag = base; st.group_cnt = base + rows; st.group_flag = st.group_cnt + g; st.ckpt_flag = st.group_flag + g;
-    st.flag_words = rs_status_flag_words(rows);
-    st.agg = base + st.flag_words; st.group = st.agg + rows * stride; st.ckpt = st.group + g * stride;
+    st.groups = rs_status_groups(rows);
+    st.agg = base; st.group = base + rows * stride; st.ckpt = st.group + st.groups * stride;
     return st;
 }
-__device__ __forceinline__ void st_cg_u32(uint32_t* p, uint32_t v) { asm volatile("st.global.cg.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 
-// Exclusive prefixes (over all tiles in front of `tile`) of the DPT digits of this thread.  total[]: this tile's counts.
-// Called by all threads of the CTA; contains barriers.
 template <int DPT, int BINS>
 __device__ __forceinline__ void tile_prefix(const RsStatus& st, long long tile, long long n_tiles, int stride, uint32_t mask,
-                                            const uint32_t (&total)[DPT], uint32_t (&prefix)[DPT], uint32_t* s_word) {
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+                                            const uint32_t (&total)[DPT], uint32_t (&prefix)[DPT]) {
+    const int t = threadIdx.x;
     const long long g = tile / RS_GROUP;
     const int r = (int)(tile - g * RS_GROUP);
     const long long g_first = g * RS_GROUP;
     const int gsize = (int)((n_tiles - g_first < RS_GROUP) ? (n_tiles - g_first) : RS_GROUP);
+    const bool last_of_group = (r == gsize - 1);
     bool exists[DPT];
+    uint32_t sum_agg[DPT];
 #pragma unroll
     for (int j = 0; j < DPT; ++j) {
         const int d = t * DPT + j;
         exists[j] = d < BINS && (uint32_t)d <= mask;  // digits above the mask do not exist in this pass
-        if (exists[j]) st_cg_u32(st.agg + tile * stride + d, total[j]);
-        prefix[j] = 0;
+        if (exists[j]) st_volatile_u32(st.agg + tile * stride + d, RS_READY | total[j]);
+        prefix[j] = 0; sum_agg[j] = 0;
     }
-    __threadfence();
-    __syncthreads();
-    if (t == 0) {
-        st_volatile_u32(st.tile_flag + tile, 1u);
-        s_word[0] = (atomicAdd(st.group_cnt + g, 1u) == (uint32_t)(gsize - 1)) ? 1u : 0u;
-    }
-    __syncthreads();
-    if (s_word[0]) {  // this tile completes its group: every row of the group is published (counter after fence)
-        __threadfence();
+    bool any = false;
 #pragma unroll
-        for (int j = 0; j < DPT; ++j) {
-            if (exists[j]) {
-                const int d = t * DPT + j;
-                uint32_t sum = 0;
-#pragma unroll 4
-                for (int i = 0; i < gsize; ++i) sum += ld_volatile_u32(st.agg + (g_first + i) * stride + d);
-                st_cg_u32(st.group + g * stride + d, sum);
+    for (int j = 0; j < DPT; ++j) any = any || exists[j];
+    if (!any) return;
+    // ---- the rows of the tiles in front of this one in its group
+    if (r > 0) {
+        uint32_t got[DPT];
+        const uint32_t want = (1u << r) - 1u;
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) got[j] = exists[j] ? 0u : want;
+        unsigned backoff = 32;
+        while (true) {
+            // (unconditional loads from clamped rows, masked afterwards: one predicate per load exhausted the seven
+            // predicate registers of a thread)
+            uint32_t w[DPT][RS_GROUP - 1];
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                const uint32_t* col = st.agg + g_first * stride + (exists[j] ? t * DPT + j : 0);
+#pragma unroll
+                for (int i = 0; i < RS_GROUP - 1; ++i) w[j][i] = ld_volatile_u32(col + min(i, r - 1) * stride);  // (min, not a select: r is CTA-uniform and 15 selects exhaust the uniform predicate registers)
             }
-        }
-        __threadfence();
-        __syncthreads();
-        if (t == 0) st_volatile_u32(st.group_flag + g, 1u);
-    }
-    if (tile == 0) return;  // block-uniform
-    // ---- warp 0: wait for the rows this tile needs; result: the checkpoint group gp (0 = the start of the keys)
-    if (warp == 0) {
-        while (r > 0) {  // the tiles in front of this one in its group
-            const uint32_t f = (lane < r) ? ld_volatile_u32(st.tile_flag + g_first + lane) : 1u;
-            if (__all_sync(0xffffffffu, f != 0u)) break;
-            __nanosleep(100);
-        }
-        long long gp = 0;
-        if (g > 0) {
-            while (true) {
-                // lane l looks at group h = g - l: is its checkpoint there, is its GROUP row there (needed for h < g)
-                const long long h = g - lane;
-                const bool ck = (h == 0) || (h > 0 && ld_volatile_u32(st.ckpt_flag + h) != 0u);
-                const bool gr = (lane == 0) || (h >= 0 && ld_volatile_u32(st.group_flag + h) != 0u);
-                const uint32_t ckm = __ballot_sync(0xffffffffu, ck);
-                const uint32_t grm = __ballot_sync(0xffffffffu, gr);
-                if (ckm) {
-                    const int l = __ffs(ckm) - 1;                       // nearest checkpoint: group g - l
-                    const uint32_t need = (l >= 31) ? 0xffffffffu : ((2u << l) - 1u);  // GROUP rows of g-1 .. g-l
-                    if ((grm & need) == need) { gp = g - l; break; }
+            bool all = true;
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                uint32_t fresh = 0, add = 0;
+#pragma unroll
+                for (int i = 0; i < RS_GROUP - 1; ++i) {
+                    const uint32_t take = (w[j][i] >> 31) & (want >> i) & ~(got[j] >> i) & 1u;  // ready, wanted, not yet counted
+                    add += take ? (w[j][i] & ~RS_READY) : 0u;
+                    fresh |= take << i;
                 }
-                __nanosleep(100);
+                sum_agg[j] += add;
+                got[j] |= fresh;
+                all = all && (got[j] == want);
+            }
+            if (all) break;
+            // wait on ONE word - the first row that is still missing - not on the whole window
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                if (got[j] != want) {
+                    const uint32_t* word = st.agg + (g_first + (__ffs(~got[j] & want) - 1)) * stride + t * DPT + j;
+                    while (!(ld_volatile_u32(word) & RS_READY)) {
+                        __nanosleep(backoff);
+                        if (backoff < 1024) backoff *= 2;
+                    }
+                }
             }
         }
-        if (lane == 0) s_word[1] = (uint32_t)gp;
     }
-    __syncthreads();
-    __threadfence();
-    const long long gp = s_word[1];
-#pragma unroll
-    for (int j = 0; j < DPT; ++j) {
-        if (exists[j]) {
-            const int d = t * DPT + j;
-            uint32_t sum = (gp > 0) ? ld_volatile_u32(st.ckpt + gp * stride + d) : 0u;
-#pragma unroll 4
-            for (long long h = gp; h < g; ++h) sum += ld_volatile_u32(st.group + h * stride + d);
-#pragma unroll 4
-            for (int i = 0; i < r; ++i) sum += ld_volatile_u32(st.agg + (g_first + i) * stride + d);
-            prefix[j] = sum;
-        }
-    }
-    if (r == 0) {  // first tile of a group: its exclusive prefix is the checkpoint of the group
+    if (last_of_group) {
 #pragma unroll
         for (int j = 0; j < DPT; ++j)
-            if (exists[j]) st_cg_u32(st.ckpt + g * stride + t * DPT + j, prefix[j]);
-        __threadfence();
-        __syncthreads();
-        if (t == 0) st_volatile_u32(st.ckpt_flag + g, 1u);
+            if (exists[j]) st_volatile_u32(st.group + g * stride + t * DPT + j, RS_READY | (sum_agg[j] + total[j]));
+    }
+    // ---- back over the groups to the nearest checkpoint
+    if (g > 0) {
+        constexpr int WG = (DPT > 1) ? 8 : 16;  // groups per step: 2 * WG * DPT loads in flight
+        long long at[DPT];   // next group boundary to examine: CKPT[at], then GROUP[at - 1]
+        bool found[DPT];
+        uint32_t base[DPT];
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) { at[j] = g; found[j] = !exists[j]; base[j] = 0; }
+        unsigned backoff = 32;
+        while (true) {
+            uint32_t c[DPT][WG], q[DPT][WG];
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                const int col = exists[j] ? t * DPT + j : 0;
+#pragma unroll
+                for (int k = 0; k < WG; ++k) {
+                    long long hgrp = at[j] - k;  // unconditional loads from clamped rows (see above); rows below 1 are
+                    if (hgrp < 1) hgrp = 1;      // never consumed: the walk ends at group boundary 0
+                    c[j][k] = ld_volatile_u32(st.ckpt + hgrp * stride + col);
+                    q[j][k] = ld_volatile_u32(st.group + (hgrp - 1) * stride + col);
+                }
+            }
+            bool all = true, progress = false;
+#pragma unroll
+            for (int j = 0; j < DPT; ++j) {
+                bool stop = found[j];
+#pragma unroll
+                for (int k = 0; k < WG; ++k) {
+                    if (!stop) {
+                        if (at[j] == 0) { found[j] = true; stop = true; }               // start of the keys
+                        else if (c[j][k] & RS_READY) { base[j] += c[j][k] & ~RS_READY; found[j] = true; stop = true; progress = true; }
+                        else if (q[j][k] & RS_READY) { base[j] += q[j][k] & ~RS_READY; at[j] -= 1; progress = true; }
+                        else stop = true;                                               // not there yet
+                    }
+                }
+                if (!found[j] && at[j] == 0) found[j] = true;
+                all = all && found[j];
+            }
+            if (all) break;
+            if (!progress) {  // blocked: wait on the two words at the boundary, not on the whole window
+#pragma unroll
+                for (int j = 0; j < DPT; ++j) {
+                    if (!found[j]) {
+                        const uint32_t* cw = st.ckpt + at[j] * stride + t * DPT + j;
+                        const uint32_t* qw = st.group + (at[j] - 1) * stride + t * DPT + j;
+                        while (!((ld_volatile_u32(cw) | ld_volatile_u32(qw)) & RS_READY)) {
+                            __nanosleep(backoff);
+                            if (backoff < 1024) backoff *= 2;
+                        }
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) prefix[j] = base[j];
+    }
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) prefix[j] += sum_agg[j];
+    if (last_of_group && g_first + gsize < n_tiles) {  // the checkpoint of the next group
+#pragma unroll
+        for (int j = 0; j < DPT; ++j)
+            if (exists[j]) st_volatile_u32(st.ckpt + (g + 1) * stride + t * DPT + j, RS_READY | (prefix[j] + total[j]));
     }
 }
 
@@ -506,9 +544,8 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
     __shared__ uint32_t s_bin_base[S][BINS];
     __shared__ uint32_t s_tmp[RS_WARPS + 1];
     __shared__ uint32_t s_tile;
-    __shared__ uint32_t s_word[2];
     const RsStatus st = rs_status_carve(status_cur, status_rows, row_stride);
-    const long long next_flag_words = rs_status_flag_words(status_rows);
+    const RsStatus stn = rs_status_carve(status_next, status_rows, row_stride);
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const bool no_lookback = (bits & 0x100) != 0;  // timing experiments only (GSR_DEBUG_NO_LOOKBACK)
@@ -544,6 +581,10 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
     if (span > span_max) span = span_max;
     if (span < 256) span = 256;
     const long long n_tiles = (n + span - 1) / span;
+    // the next pass has at most as many keys, hence at most this many tiles (and never more than status_rows)
+    long long rows_next = G * (waves > 0 ? waves : 1) + 1;
+    if (rows_next > status_rows) rows_next = status_rows;
+    const long long groups_next = rows_next / RS_GROUP + 2;
 
     while (true) {
         if (t == 0) s_tile = atomicAdd(ticket, 1u);
@@ -552,7 +593,13 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
         const long long super_base = tile * span;
         if (super_base >= n) break;
         const long long super_end = (super_base + span < n) ? super_base + span : n;
-        for (long long j = tile * RS_THREADS + t; j < next_flag_words; j += n_tiles * RS_THREADS) status_next[j] = 0;  // flags of the next pass
+        // the status words of the next pass start at zero: its AGG rows [0, rows_next) and, behind the status_rows AGG rows
+        // of the buffer, all GROUP rows and the CKPT rows [0, groups_next) - one loop over the two row ranges (two loops
+        // made ptxas fail its register allocation, C7600)
+        for (long long idx = tile; idx < rows_next + stn.groups + groups_next; idx += n_tiles) {
+            const long long row = idx < rows_next ? idx : status_rows + (idx - rows_next);
+            for (int j = t; j < row_stride; j += RS_THREADS) status_next[row * row_stride + j] = 0;
+        }
         constexpr int per_sub = ITEMS * RS_THREADS;
         uint32_t cnt[S][DPT];   // digit d of sub-tile s: keys
         int sub_out[S];         // keys parked by sub-tile s
@@ -680,7 +727,7 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             for (int sub = 0; sub < S; ++sub) total[j] += cnt[sub][j];
             prefix[j] = 0;
         }
-        if (!no_lookback) tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix, s_word);
+        if (!no_lookback) tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix);
 #pragma unroll
         for (int j = 0; j < DPT; ++j) {
             const int d = t * DPT + j;
@@ -764,7 +811,6 @@ int radix_sort_prepare_device() {
     ok = rs3_prepare_one<8, false, false>() && ok;
     ok = rs3_prepare_one<9, false, false>() && ok;
     ok = rs3_prepare_one<8, true, false>() && ok;
-    ok = rs3_prepare_one<9, true, false>() && ok;
     ok = rs3_prepare_one<8, true, true>() && ok;
     ok = rs3_prepare_one<9, true, true>() && ok;
     int nb = 0;
@@ -844,10 +890,14 @@ void sort_scratch_clear(SortScratch* scratch, long long upper, bool hist_ready, 
     if (hist_ready) {
         // the digit histograms come from the caller (k_preprocess / k_tile_scan): clear the tickets and the look-back
         // rows of the first pass only
-        // 32-bit keys: the flag words of the first pass (k_rs_pass3); 64-bit keys: its look-back rows (k_rs_pass)
+        // 32-bit keys: the AGG / GROUP / CKPT rows of the first pass (k_rs_pass3); 64-bit keys: its look-back rows (k_rs_pass)
         size_t words;
-        if (sizeof(KeyT) == 4) words = (size_t)rs_status_flag_words(scratch->max_tiles);
-        else words = (size_t)((upper + RS_THREADS * RsCfg<KeyT>::LARGE - 1) / (RS_THREADS * RsCfg<KeyT>::LARGE)) * 256;
+        if (sizeof(KeyT) == 4) {
+            long long g, rows;
+            const int stride = plan_row_stride(opt);
+            rs3_shape(upper, stride > 256 ? rs3_span(9) : rs3_span(8), &g, &rows);
+            words = (size_t)rs_status_rows_total(rows) * stride;
+        } else words = (size_t)((upper + RS_THREADS * RsCfg<KeyT>::LARGE - 1) / (RS_THREADS * RsCfg<KeyT>::LARGE)) * 256;
         cudaMemsetAsync(scratch->tickets, 0, 64 * sizeof(uint32_t), stream);
         cudaMemsetAsync(scratch->status[0], 0, words * sizeof(uint32_t), stream);
     } else {
@@ -905,7 +955,7 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
         long long g = (upper + RS_THREADS * 8 - 1) / (RS_THREADS * 8);
         if (g > sms * 8) g = sms * 8;
         if (g < 1) g = 1;
-        const long long clear_words = (sizeof(KeyT) == 4) ? rs_status_flag_words(scratch->max_tiles) : rows0 * 256;
+        const long long clear_words = (sizeof(KeyT) == 4) ? rs_status_rows_total(rows0) * row_stride : rows0 * 256;
         k_rs_hist<KeyT><<<(unsigned)g, RS_THREADS, 0, stream>>>(keys_first, n_host, n_dev, capacity, passes, scratch->hist,
                                                                scratch->status[0], clear_words);
         if (launch_count) ++*launch_count;
@@ -924,12 +974,12 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
             const int bits = passes.bits[p] | dbg_no_lb, shift = passes.shift[p];
             const RsRebase rb = {opt ? opt->k0 : 0u, opt ? opt->khi : 0xFFFFFFFFu};
 #define RS3_GO(B, I, D) rs3_launch<B, I, D>((unsigned)grid, stream, kin, kout, vin, vout, n_host, nd, capacity, shift, bits, hist_p, \
-                                           scratch->tickets + p, st_cur, st_next, row_stride, span_max, scratch->max_tiles, rb)
+                                           scratch->tickets + p, st_cur, st_next, row_stride, span_max, rows0, rb)
             const int nb = passes.bits[p];
             if (p == 0 && drop) {  // compacting first pass (identity values)
                 if (nb > 8) RS3_GO(9, true, true); else RS3_GO(8, true, true);
             } else if (identity) {
-                if (nb > 8) RS3_GO(9, true, false); else RS3_GO(8, true, false);
+                RS3_GO(8, true, false);  // (identity values with 9-bit digits only occur in the compacting pass above)
             } else if (nb > 8) RS3_GO(9, false, false);
             else if (nb == 8) RS3_GO(8, false, false);
             else if (nb == 7) RS3_GO(7, false, false);

@@ -70,6 +70,35 @@ def main():
         t0 = time.perf_counter()
         r.load_ply(p)
         t_file = time.perf_counter() - t0
+    # the whole file, end to end: B200Renderer.load_ply(path) (header parse + mapped body + chunked upload + decode)
+    # with the page cache warm and, where the box lets us drop it, cold; the NumPy port beside it
+    full = {}
+    with tempfile.TemporaryDirectory() as td:
+        p = os.path.join(td, "full.ply")
+        hdr = "ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % n
+        hdr += "".join(f"property float {nm}\n" for nm in names) + "end_header\n"
+        with open(p, "wb") as f:
+            f.write(hdr.encode())
+            f.write(rows.tobytes())
+        r.load_ply(p)
+        ts = []
+        for _ in range(3):
+            t0 = time.perf_counter(); r.load_ply(p); ts.append(time.perf_counter() - t0)
+        full["device_from_file_warm_s"] = min(ts)
+        try:
+            os.sync()
+            with open("/proc/sys/vm/drop_caches", "w") as f:
+                f.write("3\n")
+            t0 = time.perf_counter(); r.load_ply(p); full["device_from_file_cold_s"] = time.perf_counter() - t0
+        except Exception as e:
+            full["device_from_file_cold_s"] = None
+            full["cold_note"] = f"page cache could not be dropped here ({type(e).__name__})"
+        t0 = time.perf_counter()
+        with np.errstate(all="ignore"):
+            util_gau.load_ply(p)
+        full["cpu_load_ply_s"] = time.perf_counter() - t0
+        full["n"] = n
+        full["file_bytes"] = os.path.getsize(p)
     peaks = {}
     try:
         with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "MEASURED_PEAKS.json")) as f:
@@ -86,6 +115,7 @@ def main():
         "alg_bytes": alg,
         "cpu_load_ply": {"n": m, "s": t_cpu, "vertices_per_s": m / t_cpu, "kind": "port (util_gau.load_ply, NumPy)"},
         "device_load_ply_from_file": {"n": m, "s": t_file, "vertices_per_s": m / t_file},
+        "whole_file": full,
         "peaks": peaks,
     }
     print(json.dumps(line))

@@ -9,6 +9,10 @@ frames = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 g = scenes.synthetic_gaussians(n, seed=0)
 cam, pose = scenes.default_view(W, H)
 r = B200Renderer(W, H)
+import os
+if os.environ.get("GSR_PROBE_NO_GRAPH"):  # kernel-by-kernel launches (ncu captures)
+    from gaussiansplattingviewer_b200 import _gsr
+    r.tune(_gsr.GSR_TUNE_GRAPH, 0)
 r.update_gaussian_data(g)
 r.set_render_mod(3)
 r.update_camera_intrin(cam); r.update_camera_pose(cam, True, pose)
