@@ -229,6 +229,29 @@ def run_ours(args):
     ms_b = max_over_ranks(max(e0.elapsed_time(e1), wall_b))
     assert img8.shape == (H, W, 3) and img8.any()
     out = {"ms_a": ms_a, "ms_b": ms_b, "launches": launches, "t_bcast_ms": t_bcast_ms}
+    # ---- what the read-back path can carry: every rank copies a frame-sized buffer (RGB8 1080p x 10 = 62 MB) device ->
+    # pinned host at the same time, GB/s per rank (at N = 8 the GPUs share the host's PCIe switches and memory)
+    d2h_dev = torch.empty(W * H * 3 * 10, dtype=torch.uint8, device="cuda")
+    d2h_host = torch.empty(W * H * 3 * 10, dtype=torch.uint8, pin_memory=True)
+    d2h_host.copy_(d2h_dev, non_blocking=True)
+    sync_all()
+    e0.record()
+    for _ in range(8):
+        d2h_host.copy_(d2h_dev, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    d2h_gbs = 8 * d2h_dev.numel() / (e0.elapsed_time(e1) * 1e-3) / 1e9
+    if world > 1:
+        tt = torch.tensor([d2h_gbs], dtype=torch.float64, device="cuda")
+        allt = [torch.zeros_like(tt) for _ in range(world)]
+        dist.all_gather(allt, tt)
+        per = [float(x.item()) for x in allt]
+    else:
+        per = [d2h_gbs]
+    out["d2h_probe"] = {"gbs_per_rank_min": round(min(per), 2), "gbs_per_rank_median": round(float(np.median(per)), 2),
+                        "gbs_per_rank_max": round(max(per), 2), "frame_copy_ms_at_min": round(W * H * 3 / (min(per) * 1e9) * 1e3, 4),
+                        "what": "all ranks copy 62 MB device -> pinned host concurrently, 8 times"}
+    del d2h_dev, d2h_host
     # ---- config 5 (BASELINE.json configs[4]): 1024 trajectory poses over the same scene, sharded over the ranks
     out["config5"] = run_config5(r, cam, rank, world, sync_all, W, H) if args.workload == "3M_sh3_1080p" else None
     out["clocks"] = sampler.stop() if rank == 0 else None
@@ -657,7 +680,8 @@ def main():
             "peaks": {"hbm_gbs": hbm_peak, "hbm_source": peak_src, "fp32_tflops": round(fp32_peak, 2),
                       "ex2_tops": round(ex2_peak, 3), "copy_gbs_this_run": round(copy_gbs, 1)},
             "scene_broadcast_ms": round(o["t_bcast_ms"], 3)}
-    line["host"] = {"cpu_affinity_cores": len(os.sched_getaffinity(0)), "bound_to_gpu_numa_node": o.get("numa") is not None}
+    line["host"] = {"cpu_affinity_cores": len(os.sched_getaffinity(0)), "bound_to_gpu_numa_node": o.get("numa") is not None,
+                    "d2h_probe": o.get("d2h_probe")}
     # BASELINE.json's metric also names "sort Gkeys/s": the two sorts inside the frame (keys through a complete
     # key/value sort per second: 32 depth bits over N, the tile bits over D) and, at N=1, the standalone
     # gsr_sort_pairs on 2^24 random 32-bit keys with 32-bit values (all 32 bits, CUDA events, best of 5)
