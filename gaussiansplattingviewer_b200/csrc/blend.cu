@@ -22,7 +22,8 @@
 
 namespace {
 
-constexpr int BL_BATCH = 128;  // records per shared-memory batch
+constexpr int BL_BATCH = 128;  // records per shared-memory batch (64 and 256 measured 2-4 % slower)
+constexpr int BL_RUN = 8;      // hits between two checks whether the warp's pixels are all finished (4: slower, 16: same)
 struct TagTrue { static constexpr bool value = true; };
 struct TagFalse { static constexpr bool value = false; };
 
@@ -93,7 +94,7 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
     // one record = three consecutive float4 (48 B): the three shared-memory reads of a splat are constant
     // offsets from one running pointer
     __shared__ __align__(16) float4 s_rec[2][BL_BATCH][3];
-    __shared__ uint16_t s_hit[(SKIP >= 2) ? THREADS / 32 : 1][BL_BATCH];  // per-warp hit lists (SKIP >= 2)
+    __shared__ uint16_t s_hit[(SKIP >= 2) ? THREADS / 32 : 1][BL_BATCH + 2];  // per-warp hit lists (SKIP >= 2); + 2: the walk reads one entry ahead
     pdl_wait();  // may be resident behind the last radix pass: no global memory access before this
     const int W = fp->W, H = fp->H;
     const int tile = blockIdx.y * gridDim.x + blockIdx.x;
@@ -219,7 +220,12 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                 for (int k = 0; k < PPT; ++k) {
                     if constexpr (!(MODE == 0 && !COUNT && PPT % 2 == 0)) dy[k] = pyf[k] - a.y;
                     if (COUNT) n_eval += (T[k] >= 1e-4f) ? 1u : 0u;
-                    in[k] = inx && (fabsf(dy[k]) <= a.w) && (T[k] >= 1e-4f);
+                    // The shader path has no per-pixel stop (the ROP blends every fragment); a finished pixel
+                    // (T < 1e-4) only matters for the warp-level exits below, so the gaussian mode leaves the
+                    // transmittance out of the coverage predicate: one compare per pixel less, and w = alpha * T of a
+                    // finished pixel is below 1e-4 anyway
+                    constexpr bool T_TEST = !(MODE == 0 && !COUNT);
+                    in[k] = inx && (fabsf(dy[k]) <= a.w) && (!T_TEST || T[k] >= 1e-4f);
                     any_in = any_in || in[k];
                 }
                 // no live pixel of this warp lies inside the quad: skip the splat for 3 instructions
@@ -233,48 +239,58 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                     // instead of 18 + 2 + 2 + 4 scalar instructions
                     const f32x2 bdx2 = pk2(bdx, bdx), adx22 = pk2(adx2, adx2), qz2 = pk2(q.z, q.z), qw2 = pk2(q.w, q.w);
                     const f32x2 cx2 = pk2(c.x, c.x), cy2 = pk2(c.y, c.y), cz2 = pk2(c.z, c.z);
+                    // min(0.99, alpha) can only bite when opacity * 2^p2 can exceed 0.99: with p2 <= 0 guaranteed
+                    // (!CHECK_POWER) that needs an opacity above 0.99.  The record is the same for every lane, so the
+                    // branch does not diverge; two min per pixel pair less for the other splats.  (Choosing the variant
+                    // per run of eight hits instead - a 46-instruction body - measured no faster than this 50.)
+                    auto pairs = [&](auto clamp_tag) {
+                        constexpr bool CLAMP = decltype(clamp_tag)::value;
 #pragma unroll
-                    for (int k = 0; k < PPT; k += 2) {
-                        const f32x2 dy2 = pk2(dy[k], dy[k + 1]);
-                        const f32x2 p2 = fma2(fma2(qz2, dy2, bdx2), dy2, adx22);  // log2(e) * power
-                        const f32x2 ae = mul2(qw2, pk2(ex2_approx(lo2(p2)), ex2_approx(hi2(p2))));
-                        const float al0 = fminf(0.99f, lo2(ae)), al1 = fminf(0.99f, hi2(ae));
-                        const f32x2 T2 = pk2(T[k], T[k + 1]);
-                        const f32x2 aT = mul2(pk2(al0, al1), T2);
-                        float w0, w1;
-                        if (CHECK_POWER) {
-                            w0 = (in[k] && !(al0 < 1.f / 255.f) && !(lo2(p2) > 0.f)) ? lo2(aT) : 0.f;
-                            w1 = (in[k + 1] && !(al1 < 1.f / 255.f) && !(hi2(p2) > 0.f)) ? hi2(aT) : 0.f;
-                        } else {
-                            // one compare that ANDs in the coverage predicate, one select (the compiler otherwise
-                            // selects twice): w = (in && !(alpha < 1/255)) ? alpha * T : 0
-                            asm("{\n\t"
-                                ".reg .pred p, q;\n\t"
-                                "setp.ne.u32 q, %2, 0;\n\t"
-                                "setp.geu.and.f32 p, %1, 0f3B808081, q;\n\t"
-                                "selp.f32 %0, %3, 0f00000000, p;\n\t"
-                                "}"
-                                : "=f"(w0)
-                                : "f"(al0), "r"((unsigned)in[k]), "f"(lo2(aT)));
-                            asm("{\n\t"
-                                ".reg .pred p, q;\n\t"
-                                "setp.ne.u32 q, %2, 0;\n\t"
-                                "setp.geu.and.f32 p, %1, 0f3B808081, q;\n\t"
-                                "selp.f32 %0, %3, 0f00000000, p;\n\t"
-                                "}"
-                                : "=f"(w1)
-                                : "f"(al1), "r"((unsigned)in[k + 1]), "f"(hi2(aT)));
+                        for (int k = 0; k < PPT; k += 2) {
+                            const f32x2 dy2 = pk2(dy[k], dy[k + 1]);
+                            const f32x2 p2 = fma2(fma2(qz2, dy2, bdx2), dy2, adx22);  // log2(e) * power
+                            const f32x2 ae = mul2(qw2, pk2(ex2_approx(lo2(p2)), ex2_approx(hi2(p2))));
+                            float al0 = lo2(ae), al1 = hi2(ae);
+                            if (CLAMP) { al0 = fminf(0.99f, al0); al1 = fminf(0.99f, al1); }
+                            const f32x2 T2 = pk2(T[k], T[k + 1]);
+                            const f32x2 aT = mul2(pk2(al0, al1), T2);
+                            float w0, w1;
+                            if (CHECK_POWER) {
+                                w0 = (in[k] && !(al0 < 1.f / 255.f) && !(lo2(p2) > 0.f)) ? lo2(aT) : 0.f;
+                                w1 = (in[k + 1] && !(al1 < 1.f / 255.f) && !(hi2(p2) > 0.f)) ? hi2(aT) : 0.f;
+                            } else {
+                                // one compare that ANDs in the coverage predicate, one select (the compiler otherwise
+                                // selects twice): w = (in && !(alpha < 1/255)) ? alpha * T : 0
+                                asm("{\n\t"
+                                    ".reg .pred p, q;\n\t"
+                                    "setp.ne.u32 q, %2, 0;\n\t"
+                                    "setp.geu.and.f32 p, %1, 0f3B808081, q;\n\t"
+                                    "selp.f32 %0, %3, 0f00000000, p;\n\t"
+                                    "}"
+                                    : "=f"(w0)
+                                    : "f"(al0), "r"((unsigned)in[k]), "f"(lo2(aT)));
+                                asm("{\n\t"
+                                    ".reg .pred p, q;\n\t"
+                                    "setp.ne.u32 q, %2, 0;\n\t"
+                                    "setp.geu.and.f32 p, %1, 0f3B808081, q;\n\t"
+                                    "selp.f32 %0, %3, 0f00000000, p;\n\t"
+                                    "}"
+                                    : "=f"(w1)
+                                    : "f"(al1), "r"((unsigned)in[k + 1]), "f"(hi2(aT)));
+                            }
+                            const f32x2 w2 = pk2(w0, w1);
+                            const f32x2 r2 = fma2(w2, cx2, pk2(cr[k], cr[k + 1]));
+                            const f32x2 g2 = fma2(w2, cy2, pk2(cg[k], cg[k + 1]));
+                            const f32x2 b2 = fma2(w2, cz2, pk2(cb[k], cb[k + 1]));
+                            const f32x2 Tn = sub2(T2, w2);
+                            cr[k] = lo2(r2); cr[k + 1] = hi2(r2);
+                            cg[k] = lo2(g2); cg[k + 1] = hi2(g2);
+                            cb[k] = lo2(b2); cb[k + 1] = hi2(b2);
+                            T[k] = lo2(Tn); T[k + 1] = hi2(Tn);
                         }
-                        const f32x2 w2 = pk2(w0, w1);
-                        const f32x2 r2 = fma2(w2, cx2, pk2(cr[k], cr[k + 1]));
-                        const f32x2 g2 = fma2(w2, cy2, pk2(cg[k], cg[k + 1]));
-                        const f32x2 b2 = fma2(w2, cz2, pk2(cb[k], cb[k + 1]));
-                        const f32x2 Tn = sub2(T2, w2);
-                        cr[k] = lo2(r2); cr[k + 1] = hi2(r2);
-                        cg[k] = lo2(g2); cg[k + 1] = hi2(g2);
-                        cb[k] = lo2(b2); cb[k + 1] = hi2(b2);
-                        T[k] = lo2(Tn); T[k + 1] = hi2(Tn);
-                    }
+                    };
+                    if (CHECK_POWER || q.w > 0.98f) pairs(TagTrue{});
+                    else pairs(TagFalse{});
                     return;
                 }
 #pragma unroll
@@ -386,7 +402,7 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                     n_hit_w += __popc(hit);
                 }
                 __syncwarp();
-                for (int h0 = 0; h0 < n_hit_w; h0 += 8) {
+                for (int h0 = 0; h0 < n_hit_w; h0 += BL_RUN) {
                     // pixels die as the batch goes on: re-check every 8 hits
                     if (h0) {
                         bool alive = false;
@@ -394,9 +410,16 @@ __global__ void __launch_bounds__(TILE * TILE / PPT) k_blend(const FrameParams* 
                         for (int k = 0; k < PPT; ++k) alive = alive || (T[k] >= 1e-4f);
                         if (!__any_sync(0xffffffffu, alive)) break;
                     }
-                    const int h1 = min(h0 + 8, n_hit_w);
+                    const int h1 = min(h0 + BL_RUN, n_hit_w);
+                    // the next entry's offset is fetched while this splat is blended: the LDS.U16 -> LDS.128 pair at
+                    // the head of every splat's dependency chain becomes one shared-memory latency (-1.7 % kernel time)
+                    unsigned rec_next = lds16(hl_base + 2 * h0);
 #pragma unroll 1
-                    for (unsigned p = hl_base + 2 * h0, pe = hl_base + 2 * h1; p != pe; p += 2) splat(lds16(p));
+                    for (unsigned p = hl_base + 2 * h0, pe = hl_base + 2 * h1; p != pe; p += 2) {
+                        const unsigned rec = rec_next;
+                        rec_next = lds16(p + 2);
+                        splat(rec);
+                    }
                 }
             } else {
 #pragma unroll 2

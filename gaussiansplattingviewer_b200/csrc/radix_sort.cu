@@ -548,8 +548,6 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
     const RsStatus stn = rs_status_carve(status_next, status_rows, row_stride);
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const bool no_lookback = (bits & 0x100) != 0;  // timing experiments only (GSR_DEBUG_NO_LOOKBACK)
-    bits &= 0xff;
     const uint32_t mask = (1u << bits) - 1u;
     const uint32_t lt_mask = (1u << lane) - 1u;
     pdl_wait();  // resident behind the previous pass; nothing of global memory is touched before this
@@ -727,7 +725,7 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             for (int sub = 0; sub < S; ++sub) total[j] += cnt[sub][j];
             prefix[j] = 0;
         }
-        if (!no_lookback) tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix);
+        tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix);
 #pragma unroll
         for (int j = 0; j < DPT; ++j) {
             const int d = t * DPT + j;
@@ -777,7 +775,6 @@ int num_sms() {  // of the CURRENT device (a process may hold handles on several
 constexpr int RS3_S = 2, RS3_MINB = 3;
 constexpr int rs3_items(int bits) { return bits > 8 ? 15 : 16; }
 constexpr int rs3_span(int bits) { return RS3_S * rs3_items(bits) * RS_THREADS; }  // 7680 / 8192 keys
-constexpr int RS3_SPAN_MIN = rs3_span(9);
 
 template <int BITS, bool IDENT, bool DROP>
 void rs3_launch(unsigned grid, cudaStream_t stream, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
@@ -844,10 +841,9 @@ void rs3_shape(long long upper, int span_max, long long* grid, long long* rows) 
 }
 }  // namespace
 
-// Look-back rows: the buffers are sized in rows of RS_ROW_WORDS words.  A 32-bit-key sort over max_items keys uses at
+// Look-back rows: the buffers are sized in rows of 512 words.  A 32-bit-key sort over max_items keys uses at
 // most max_items / 7680 + resident CTAs + 1 rows of 256 or 512 words (rs3_shape), a 64-bit-key sort max_items / 3072
 // rows of 256 words.
-constexpr int RS_ROW_WORDS = 512;
 constexpr long long scratch_rows(long long max_items) { return max_items / 6144 + 3 * 192 + 4; }  // 3 resident CTAs per SM, <= 192 SMs
 
 size_t sort_scratch_bytes(long long max_items, int /*key_bytes*/) {
@@ -970,8 +966,7 @@ int radix_sort_pairs(const KeyT* keys_first, KeyT* keys, KeyT* keys_tmp, uint32_
         const uint32_t* hist_p = scratch->hist + p * hist_stride;
         if constexpr (sizeof(KeyT) == 4) {
             const uint32_t* nd = (p > 0 && opt && opt->n_dev_rest) ? opt->n_dev_rest : n_dev;
-            static const int dbg_no_lb = getenv("GSR_DEBUG_NO_LOOKBACK") ? 0x100 : 0;
-            const int bits = passes.bits[p] | dbg_no_lb, shift = passes.shift[p];
+            const int bits = passes.bits[p], shift = passes.shift[p];
             const RsRebase rb = {opt ? opt->k0 : 0u, opt ? opt->khi : 0xFFFFFFFFu};
 #define RS3_GO(B, I, D) rs3_launch<B, I, D>((unsigned)grid, stream, kin, kout, vin, vout, n_host, nd, capacity, shift, bits, hist_p, \
                                            scratch->tickets + p, st_cur, st_next, row_stride, span_max, rows0, rb)

@@ -75,7 +75,7 @@ def test_synchronous_overflow_does_not_poison_the_pipelined_path(R):
 
 def test_more_than_65536_tiles(R):
     """17 tile bits (4096 x 4352 with 16-px tiles): k_tile_scan keeps out of the sort histograms, the tile sort
-    counts its digits itself; image identical to the 32-px tiling (16 bits, histogram from the scan)."""
+    counts its digits itself; image equal to the 32-px tiling (16 bits, histogram from the scan)."""
     g = scenes.synthetic_gaussians(60000, seed=43)
     W, H = 4096, 4352
     r, _, _ = _renderer(R, g, W, H)
@@ -86,9 +86,11 @@ def test_more_than_65536_tiles(R):
     b = r.draw().cpu().numpy()
     s = r.stats()
     assert s.tiles_x * s.tiles_y == 256 * 272 > 65536 and not s.overflow
-    assert np.array_equal(_bits(a), _bits(b))
+    # same splats in the same order per pixel; a finished pixel keeps blending until its warp is finished, and the
+    # warps of a 16-px tile are not those of a 32-px tile: below 1e-4 per channel (tests/test_gpu_parity.py)
+    assert np.abs(a - b).max() <= 2e-4
     b2 = r.draw().cpu().numpy()             # the forked (untimed) path twice: no stale histogram
-    assert np.array_equal(_bits(a), _bits(b2))
+    assert np.array_equal(_bits(b), _bits(b2))
 
 
 def test_gaussian_order_keeps_a_frozen_order(R):
