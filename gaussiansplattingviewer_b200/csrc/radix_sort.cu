@@ -163,7 +163,7 @@ __host__ __device__ inline RsStatus rs_status_carve(uint32_t* base, long long ro
 }
 
 template <int DPT, int BINS>
-__device__ __forceinline__ void tile_prefix(const RsStatus& st, long long tile, long long n_tiles, int stride, uint32_t mask,
+__device__ __forceinline__ void tile_prefix_thread(const RsStatus& st, long long tile, long long n_tiles, int stride, uint32_t mask,
                                             const uint32_t (&total)[DPT], uint32_t (&prefix)[DPT]) {
     const int t = threadIdx.x;
     const long long g = tile / RS_GROUP;
@@ -290,6 +290,201 @@ __device__ __forceinline__ void tile_prefix(const RsStatus& st, long long tile, 
 #pragma unroll
         for (int j = 0; j < DPT; ++j) prefix[j] = base[j];
     }
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) prefix[j] += sum_agg[j];
+    if (last_of_group && g_first + gsize < n_tiles) {  // the checkpoint of the next group
+#pragma unroll
+        for (int j = 0; j < DPT; ++j)
+            if (exists[j]) st_volatile_u32(st.ckpt + (g + 1) * stride + t * DPT + j, RS_READY | (prefix[j] + total[j]));
+    }
+}
+
+
+#ifdef GSR_RS_TRACE  // development only: globaltimer stamps of the first super-tile of every CTA, per pass of a frame
+__device__ unsigned long long g_rs_trace[5 * 1024 * 10];
+__device__ unsigned long long g_rs_trace2[5 * 1024 * 10];
+__device__ int g_rs_slot_dummy;
+#define RS_P(i, val) do { if (threadIdx.x == 0 && tr_on && blockIdx.x < 1024) g_rs_trace2[(tr_slot * 1024 + blockIdx.x) * 10 + (i)] = (val); } while (0)
+__device__ __forceinline__ unsigned long long rs_now() { unsigned long long v; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v)); return v; }
+#define RS_T(i) do { if (threadIdx.x == 0 && rs_first && blockIdx.x < 1024) g_rs_trace[(rs_slot * 1024 + blockIdx.x) * 10 + (i)] = rs_now(); } while (0)
+#else
+#define RS_T(i) do { } while (0)
+#define RS_P(i, val) do { } while (0)
+#endif
+
+__device__ __forceinline__ uint4 ld_volatile_v4(const uint32_t* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+// The walk is done by the CTA as a whole (globaltimer trace of the per-thread version, scripts/probe_rs_trace.py: in a
+// single-wave pass the prefix of a tile was known 10-12 us after the last tile in front of it had counted - five
+// dependent round trips of up to 32 scalar loads per thread, with all 113 k threads of the grid polling).  One STEP reads
+// up to 16 rows with 128-bit loads spread over the 256 threads (a thread keeps one column of four digits and rows
+// row0, row0 + rpt, ...), an OR over the CTA tells which rows are complete, the leading complete rows are summed in
+// registers, and the owners of the digits add up the partial columns out of shared memory.  A blocked CTA waits with ONE
+// thread polling one word.
+//   s_part: RS_THREADS * 4 words, s_ctl: 2 words of shared memory.
+template <int DPT, int BINS>
+__device__ __forceinline__ void tile_prefix(const RsStatus& st, long long tile, long long n_tiles, int stride, uint32_t mask,
+                                            const uint32_t (&total)[DPT], uint32_t (&prefix)[DPT], uint32_t* s_part,
+                                            uint32_t* s_ctl, int tr_slot = 0, bool tr_on = false) {
+    (void)tr_slot; (void)tr_on;
+    unsigned long long n_steps = 0, n_waits = 0; (void)n_steps; (void)n_waits;
+    RS_P(0, rs_now());
+    constexpr int NCOL_MAX = (BINS >= 4) ? BINS / 4 : 1;
+    constexpr int L = (16 * NCOL_MAX > RS_THREADS) ? 16 * NCOL_MAX / RS_THREADS : 1;  // 512 bins: 8, 256: 4, 128: 2, else 1
+    const int t = threadIdx.x;
+    const long long g = tile / RS_GROUP;
+    const int r = (int)(tile - g * RS_GROUP);
+    const long long g_first = g * RS_GROUP;
+    const int gsize = (int)((n_tiles - g_first < RS_GROUP) ? (n_tiles - g_first) : RS_GROUP);
+    const bool last_of_group = (r == gsize - 1);
+    bool exists[DPT];
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) {
+        const int d = t * DPT + j;
+        exists[j] = d < BINS && (uint32_t)d <= mask;  // digits above the mask do not exist in this pass
+        if (exists[j]) st_volatile_u32(st.agg + tile * stride + d, RS_READY | total[j]);
+        prefix[j] = 0;
+    }
+    if (tile == 0) return;  // CTA-uniform: nothing in front (a group of one tile has no GROUP / CKPT reader either)
+    const int nd = (int)mask + 1;
+    const int cshift = (nd >= 4) ? (29 - __clz(nd)) : 0;  // log2 of the number of four-word columns of a row
+    const int ncol = 1 << cshift;
+    const int col = t & (ncol - 1), row0 = t >> cshift, rpt = RS_THREADS >> cshift;
+    const int nparts = rpt < 16 ? rpt : 16;  // partial columns that can hold a row
+    uint32_t ex = 0;                          // which of the four words of this thread's column are digits of the pass
+#pragma unroll
+    for (int w = 0; w < 4; ++w) ex |= ((uint32_t)(4 * col + w) <= mask) ? (1u << w) : 0u;
+    if (t == 0) { s_ctl[0] = 0u; s_ctl[1] = 0u; }
+    __syncthreads();
+    int par = 0;
+    uint4 v[L];
+    // loads rows i = 0 .. n_rows - 1 (row i at ptr(i)); returns a CTA-uniform mask of the rows that are NOT complete yet
+    auto load_rows = [&](auto ptr, int n_rows) -> uint32_t {
+        uint32_t missing = 0;
+        // every load of the step is issued before the first one is looked at (a warp issues in order: a consumer right
+        // behind its load makes the step L dependent round trips - measured: 4.8 us instead of 1)
+#pragma unroll
+        for (int k = 0; k < L; ++k) {
+            const int i = row0 + k * rpt;
+            if (i < n_rows) v[k] = ld_volatile_v4(ptr(i) + 4 * col);
+            else v[k] = make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < L; ++k) {
+            const int i = row0 + k * rpt;
+            const uint32_t rdy = (v[k].x >> 31) | ((v[k].y >> 31) << 1) | ((v[k].z >> 31) << 2) | ((v[k].w >> 31) << 3);
+            if (i < n_rows && (rdy & ex) != ex) missing |= 1u << i;
+        }
+        missing = __reduce_or_sync(0xffffffffu, missing);
+        if ((t & 31) == 0) {
+            if (missing) atomicOr(&s_ctl[par], missing);
+        }
+        if (t == 0) s_ctl[par ^ 1] = 0u;
+        __syncthreads();
+        const uint32_t m = s_ctl[par];
+        par ^= 1;
+        return m;
+    };
+    // this thread's column summed over the rows [lo, hi) of the last load
+    auto sum_rows = [&](int lo, int hi) -> uint4 {
+        uint4 a = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int k = 0; k < L; ++k) {
+            const int i = row0 + k * rpt;
+            if (i >= lo && i < hi) {
+                a.x += v[k].x & ~RS_READY; a.y += v[k].y & ~RS_READY; a.z += v[k].z & ~RS_READY; a.w += v[k].w & ~RS_READY;
+            }
+        }
+        return a;
+    };
+    // partial columns -> the owners of the digits
+    auto to_owners = [&](const uint4& a, uint32_t (&dst)[DPT]) {
+        if (row0 < nparts) reinterpret_cast<uint4*>(s_part)[row0 * ncol + col] = a;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < DPT; ++j) {
+            if (exists[j]) {
+                uint32_t acc = 0;
+                for (int q = 0; q < nparts; ++q) acc += s_part[q * (4 * ncol) + t * DPT + j];
+                dst[j] += acc;
+            }
+        }
+        // (s_part is written again only behind the barrier of the next load_rows)
+    };
+    auto wait_for = [&](const uint32_t* w0, const uint32_t* w1) {  // one thread polls; digit 0 exists in every pass
+        if (t == 0) {
+            unsigned backoff = 32;
+            while (!((ld_volatile_u32(w0) | (w1 ? ld_volatile_u32(w1) : 0u)) & RS_READY)) {
+                __nanosleep(backoff);
+                if (backoff < 512) backoff *= 2;
+            }
+        }
+        __syncthreads();
+    };
+
+    // ---- the rows of the tiles in front of this one in its group: tile - 1, tile - 2, ..., g_first
+    uint32_t sum_agg[DPT];
+#pragma unroll
+    for (int j = 0; j < DPT; ++j) sum_agg[j] = 0;
+    {
+        long long top = tile - 1;
+        int need = r;
+        while (need > 0) {
+            const uint32_t* row_top = st.agg + top * stride;
+            const uint32_t missing = load_rows([&](int i) { return row_top - (long long)i * stride; }, need);
+            ++n_steps;
+            int run = missing ? __ffs(missing) - 1 : need;
+            if (run > need) run = need;
+            if (run > 0) {
+                to_owners(sum_rows(0, run), sum_agg);
+                top -= run; need -= run;
+            } else {
+                ++n_waits;
+                wait_for(row_top, nullptr);
+            }
+        }
+    }
+    RS_P(1, rs_now()); RS_P(5, n_steps | (n_waits << 32)); n_steps = 0; n_waits = 0;
+    if (last_of_group) {
+#pragma unroll
+        for (int j = 0; j < DPT; ++j)
+            if (exists[j]) st_volatile_u32(st.group + g * stride + t * DPT + j, RS_READY | (sum_agg[j] + total[j]));
+    }
+    bool tr_firststep = true; (void)tr_firststep;
+    // ---- back over the groups to the nearest checkpoint: row 0 of a step is CKPT[at], rows 1.. are GROUP[at - 1], ...
+    // (letting only the group's publisher walk and the other tiles wait for their checkpoint was measured: a third less
+    // status traffic, but the extra publish -> poll -> read hop costs more, depth sort 0.108 -> 0.112 ms)
+    {
+        long long at = g;
+        while (at > 0) {
+            const int n_rows = (int)((at + 1 < 16) ? at + 1 : 16);
+            const uint32_t* ck = st.ckpt + at * stride;
+            const uint32_t* gr = st.group + at * stride;
+            const uint32_t missing = load_rows([&](int i) { return i == 0 ? ck : gr - (long long)i * stride; }, n_rows);
+            ++n_steps;
+            if (tr_firststep) { RS_P(2, rs_now()); tr_firststep = false; }
+            if (!(missing & 1u)) {  // the checkpoint is there
+                to_owners(sum_rows(0, 1), prefix);
+                break;
+            }
+            const uint32_t mg = missing >> 1;
+            int run = mg ? __ffs(mg) - 1 : n_rows - 1;
+            if (run > n_rows - 1) run = n_rows - 1;
+            if (run > 0) {
+                to_owners(sum_rows(1, 1 + run), prefix);
+                at -= run;
+            } else {
+                ++n_waits;
+                wait_for(ck, gr - stride);
+                RS_P(3, rs_now());
+            }
+        }
+    }
+    RS_P(4, rs_now()); RS_P(6, n_steps | (n_waits << 32)); RS_P(7, (unsigned long long)last_of_group);
 #pragma unroll
     for (int j = 0; j < DPT; ++j) prefix[j] += sum_agg[j];
     if (last_of_group && g_first + gsize < n_tiles) {  // the checkpoint of the next group
@@ -525,6 +720,7 @@ __global__ void __launch_bounds__(RS_THREADS, (ITEMS <= 8 ? 5 : 3)) k_rs_pass(co
 //           passes over all of them).
 struct RsRebase { uint32_t k0, khi; };
 
+
 template <int BITS, int ITEMS, int S, int MINB, bool IDENTITY_VALS, bool DROP>
 __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                                                           const uint32_t* __restrict__ vals_in,
@@ -544,13 +740,23 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
     __shared__ uint32_t s_bin_base[S][BINS];
     __shared__ uint32_t s_tmp[RS_WARPS + 1];
     __shared__ uint32_t s_tile;
+    __shared__ uint32_t s_ctl[2];
+    // partial columns of tile_prefix: the per-warp counters are free by then (they are 4 KB from 256 bins on)
+    __shared__ __align__(16) uint32_t s_part_small[4];  // (narrower digits would need RS_THREADS * 4 words of their own)
+    uint32_t* const s_part = (BINS >= 512) ? reinterpret_cast<uint32_t*>(s_whist) : s_part_small;
     const RsStatus st = rs_status_carve(status_cur, status_rows, row_stride);
     const RsStatus stn = rs_status_carve(status_next, status_rows, row_stride);
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const uint32_t mask = (1u << bits) - 1u;
     const uint32_t lt_mask = (1u << lane) - 1u;
+#ifdef GSR_RS_TRACE
+    const int rs_slot = (bits == 9) ? shift / 9 : (shift > 0 ? 4 : 3);
+    bool rs_first = true;
+    RS_T(0);
+#endif
     pdl_wait();  // resident behind the previous pass; nothing of global memory is touched before this
+    RS_T(1);
     long long n = n_dev ? (long long)(*n_dev) : n_host;
     if (n > capacity) n = capacity;
 
@@ -580,16 +786,30 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
     if (span < 256) span = 256;
     const long long n_tiles = (n + span - 1) / span;
     // the next pass has at most as many keys, hence at most this many tiles (and never more than status_rows)
-    long long rows_next = G * (waves > 0 ? waves : 1) + 1;
+    // (its instance may cut shorter spans than this one: count with the shortest span any instance uses)
+    const long long span_floor = span_max < 27 * RS_THREADS ? span_max : 27 * RS_THREADS;
+    const long long waves_next = (n + G * span_floor - 1) / (G * span_floor);
+    long long rows_next = G * (waves_next > 0 ? waves_next : 1) + 1;
     if (rows_next > status_rows) rows_next = status_rows;
     const long long groups_next = rows_next / RS_GROUP + 2;
 
     while (true) {
+        // (drawn behind the histogram scan on purpose: CTAs that get going first take the spans in front, so a tile
+        // rarely waits for a slower predecessor; drawing the first ticket before the scan, beside the histogram loads, cost
+        // 5 us per sort)
         if (t == 0) s_tile = atomicAdd(ticket, 1u);
         __syncthreads();
         const long long tile = s_tile;  // super-tile index
         const long long super_base = tile * span;
         if (super_base >= n) break;
+        RS_T(2);
+#ifdef GSR_RS_TRACE
+        if (threadIdx.x == 0 && rs_first && blockIdx.x < 1024) {
+            unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            g_rs_trace[(rs_slot * 1024 + blockIdx.x) * 10 + 8] = ((unsigned long long)smid << 32) | (unsigned long long)tile;
+            g_rs_trace[(rs_slot * 1024 + blockIdx.x) * 10 + 9] = (unsigned long long)n_tiles;
+        }
+#endif
         const long long super_end = (super_base + span < n) ? super_base + span : n;
         // the status words of the next pass start at zero: its AGG rows [0, rows_next) and, behind the status_rows AGG rows
         // of the buffer, all GROUP rows and the CKPT rows [0, groups_next) - one loop over the two row ranges (two loops
@@ -598,6 +818,7 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             const long long row = idx < rows_next ? idx : status_rows + (idx - rows_next);
             for (int j = t; j < row_stride; j += RS_THREADS) status_next[row * row_stride + j] = 0;
         }
+        RS_T(3);
         constexpr int per_sub = ITEMS * RS_THREADS;
         uint32_t cnt[S][DPT];   // digit d of sub-tile s: keys
         int sub_out[S];         // keys parked by sub-tile s
@@ -613,7 +834,10 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             for (int i = t; i < RS_WARPS * BINS / 8; i += RS_THREADS) reinterpret_cast<uint4*>(s_whist)[i] = make_uint4(0u, 0u, 0u, 0u);
             __syncthreads();
             // ---- load (warp-striped: item i of lane l is element warp_first + i*32 + l; 32-bit offsets from one pointer)
-            uint32_t key[ITEMS], val[ITEMS];
+            // more than 16 keys per thread: the values are fetched after the ranking, into the registers of the keys
+            // (key + peer mask/rank + value per item do not fit 80 registers)
+            constexpr bool DEFER_VALS = !IDENTITY_VALS && ITEMS > 16;
+            uint32_t key[ITEMS], val[DEFER_VALS ? 1 : ITEMS];
             const long long warp_first = sub_base + (long long)warp * (ITEMS * 32);
             const bool warp_has_keys = warp_first < sub_end;  // warp-uniform
             // items i with i * 32 < left hold a key of the sub-tile
@@ -626,8 +850,8 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             for (int i = 0; i < ITEMS; ++i) {
                 const bool in = i * 32 < left;
                 key[i] = in ? kp[i * 32] : 0xFFFFFFFFu;  // padding keys: digit `mask` of every pass, behind the valid keys
-                if (IDENTITY_VALS) val[i] = idx0 + i * 32;
-                else val[i] = in ? vp[i * 32] : 0u;
+                if constexpr (IDENTITY_VALS) val[i] = idx0 + i * 32;
+                else if constexpr (!DEFER_VALS) val[i] = in ? vp[i * 32] : 0u;
                 if (DROP) {
                     const bool keep = in && (key[i] != 0xFFFFFFFFu);
                     key[i] = min(max(key[i], rb.k0), rb.khi) - rb.k0;
@@ -703,19 +927,39 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             uint32_t* sv = s_vals + out_base;
             if (warp_has_keys) {
                 const uint16_t* wh = s_whist + warp * BINS;
+                // padding keys (only the last warp with keys has any; they rank behind every valid key of the last
+                // digit) are not parked: the staging area holds the span's keys and nothing else
+                if constexpr (DEFER_VALS) {
 #pragma unroll
-                for (int i = 0; i < ITEMS; ++i) {
-                    if (!DROP || ((vbits >> i) & 1u)) {  // (padding keys park behind the valid ones and are never written out)
+                    for (int i = 0; i < ITEMS; ++i) {
                         const uint32_t d = (key[i] >> shift) & mask;
                         const uint32_t pos = (uint32_t)s_digit_start[d] + wh[d] + rank[i];
-                        sk[pos] = key[i];
-                        sv[pos] = val[i];
+                        rank[i] = pos;
+                        if (i * 32 < left) sk[pos] = key[i];
+                    }
+#pragma unroll
+                    for (int i = 0; i < ITEMS; ++i) key[i] = (i * 32 < left) ? vp[i * 32] : 0u;
+#pragma unroll
+                    for (int i = 0; i < ITEMS; ++i)
+                        if (i * 32 < left) sv[rank[i]] = key[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < ITEMS; ++i) {
+                        // (these instances stage S * ITEMS * 256 keys, so padding keys may park behind the valid ones)
+                        if (!DROP || ((vbits >> i) & 1u)) {
+                            const uint32_t d = (key[i] >> shift) & mask;
+                            const uint32_t pos = (uint32_t)s_digit_start[d] + wh[d] + rank[i];
+                            sk[pos] = key[i];
+                            sv[pos] = val[i];
+                        }
                     }
                 }
             }
             out_base += sub_out[sub];
             __syncthreads();  // s_whist / s_digit_start are rewritten by the next sub-tile
+            if (sub == 0) RS_T(4);
         }
+        RS_T(5);
         // ---- one count row for the whole super-tile, then its prefix over the tiles in front (tile_prefix)
         uint32_t total[DPT], prefix[DPT];
 #pragma unroll
@@ -725,7 +969,19 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             for (int sub = 0; sub < S; ++sub) total[j] += cnt[sub][j];
             prefix[j] = 0;
         }
-        tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix);
+        // 9-bit digits (the frame's depth sort: single-wave passes, 2 KB rows) walk as a CTA; narrower digits keep the
+        // per-thread walk, which has no barriers and in a multi-wave pass finds a checkpoint at its first probe (the
+        // CTA-wide walk cost the 4K tile sort 6 us)
+        if constexpr (BINS >= 512) {
+#ifdef GSR_RS_TRACE
+            tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix, s_part, s_ctl, rs_slot, rs_first);
+#else
+            tile_prefix<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix, s_part, s_ctl);
+#endif
+        } else {
+            tile_prefix_thread<DPT, BINS>(st, tile, n_tiles, row_stride, mask, total, prefix);
+        }
+        RS_T(6);
 #pragma unroll
         for (int j = 0; j < DPT; ++j) {
             const int d = t * DPT + j;
@@ -755,8 +1011,25 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
             base += sub_out[sub];
         }
         __syncthreads();  // staging and s_bin_base are rewritten by the next super-tile
+        RS_T(7);
+#ifdef GSR_RS_TRACE
+        rs_first = false;
+#endif
     }
 }
+
+#ifdef GSR_RS_TRACE
+}  // namespace
+extern "C" __attribute__((visibility("default"))) int gsr_debug_rs_trace(unsigned long long* out, long long n_words) {
+    if (n_words > 5 * 1024 * 10) n_words = 5 * 1024 * 10;
+    return (int)cudaMemcpyFromSymbol(out, g_rs_trace, (size_t)n_words * 8);
+}
+extern "C" __attribute__((visibility("default"))) int gsr_debug_rs_trace2(unsigned long long* out, long long n_words) {
+    if (n_words > 5 * 1024 * 10) n_words = 5 * 1024 * 10;
+    return (int)cudaMemcpyFromSymbol(out, g_rs_trace2, (size_t)n_words * 8);
+}
+namespace {
+#endif
 
 int num_sms() {  // of the CURRENT device (a process may hold handles on several)
     static int cache[64] = {};
@@ -772,23 +1045,35 @@ int num_sms() {  // of the CURRENT device (a process may hold handles on several
 
 // ---- k_rs_pass3 configuration: 15 keys per thread and sub-tile, two sub-tiles, three CTAs per SM -----------------
 // 9-bit digits: 13 KB of counters per CTA leave 60 KB of staging (15 keys per thread); up to 8 bits: 16 keys
-constexpr int RS3_S = 2, RS3_MINB = 3;
-constexpr int rs3_items(int bits) { return bits > 8 ? 15 : 16; }
-constexpr int rs3_span(int bits) { return RS3_S * rs3_items(bits) * RS_THREADS; }  // 7680 / 8192 keys
+// The frame's depth sort runs single-wave passes (one super-tile per resident CTA), and the globaltimer trace of such
+// a pass (scripts/probe_rs_trace.py) shows a sub-tile costing ~5 us whether it holds 832 or 3840 keys (global-load
+// latency, four barriers, the counter scan): so those passes take their span as ONE sub-tile with more keys per thread
+// - 27 in the compacting first pass (identity values: key + rank only), 19 (+ a second sub-tile for views where more
+// Gaussians are visible) in the other two, which fetch the values after the ranking.
+constexpr int RS3_MINB = 3;
+template <int BITS, bool IDENT, bool DROP> struct Rs3Cfg {
+    static constexpr int ITEMS = BITS > 8 ? 15 : 16, S = 2, SPAN = S * ITEMS * RS_THREADS;  // 7680 / 8192 keys
+};
+template <> struct Rs3Cfg<9, true, true> { static constexpr int ITEMS = 27, S = 1, SPAN = 27 * RS_THREADS; };    // 6912 (15 x 2 measured 1 % slower)
+template <> struct Rs3Cfg<9, false, false> { static constexpr int ITEMS = 19, S = 2, SPAN = 30 * RS_THREADS; };  // 7680 (4864 + 2816)
+constexpr int rs3_span(int bits) { return bits > 8 ? 27 * RS_THREADS : 2 * 16 * RS_THREADS; }  // smallest span of a plan: sizes grid and rows
 
 template <int BITS, bool IDENT, bool DROP>
 void rs3_launch(unsigned grid, cudaStream_t stream, const uint32_t* kin, uint32_t* kout, const uint32_t* vin, uint32_t* vout,
                 long long n_host, const uint32_t* n_dev, long long capacity, int shift, int bits, const uint32_t* hist,
                 uint32_t* ticket, uint32_t* st_cur, uint32_t* st_next, int row_stride, int span_max, long long status_rows,
                 RsRebase rb) {
-    launch_pdl_m(1, k_rs_pass3<BITS, rs3_items(BITS), RS3_S, RS3_MINB, IDENT, DROP>, dim3(grid), dim3(RS_THREADS),
-                 (size_t)rs3_span(BITS) * 8, stream, kin, kout, vin, vout, n_host, n_dev, capacity, shift, bits, hist, ticket, st_cur,
-                 st_next, row_stride, span_max, status_rows, rb);
+    using Cfg = Rs3Cfg<BITS, IDENT, DROP>;
+    (void)span_max;  // every instance has its own span; the caller's figure only sizes the grid and the rows
+    launch_pdl_m(1, k_rs_pass3<BITS, Cfg::ITEMS, Cfg::S, RS3_MINB, IDENT, DROP>, dim3(grid), dim3(RS_THREADS),
+                 (size_t)Cfg::SPAN * 8, stream, kin, kout, vin, vout, n_host, n_dev, capacity, shift, bits, hist, ticket, st_cur,
+                 st_next, row_stride, (int)Cfg::SPAN, status_rows, rb);
 }
 template <int BITS, bool IDENT, bool DROP>
 bool rs3_prepare_one() {
-    const void* f = (const void*)k_rs_pass3<BITS, rs3_items(BITS), RS3_S, RS3_MINB, IDENT, DROP>;
-    return cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, rs3_span(BITS) * 8) == cudaSuccess &&
+    using Cfg = Rs3Cfg<BITS, IDENT, DROP>;
+    const void* f = (const void*)k_rs_pass3<BITS, Cfg::ITEMS, Cfg::S, RS3_MINB, IDENT, DROP>;
+    return cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SPAN * 8) == cudaSuccess &&
            cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, 100) == cudaSuccess;
 }
 int g_rs3_ctas[64] = {};  // resident CTAs per SM of the pass kernel, per device (0 = not prepared yet)
@@ -811,8 +1096,8 @@ int radix_sort_prepare_device() {
     ok = rs3_prepare_one<8, true, true>() && ok;
     ok = rs3_prepare_one<9, true, true>() && ok;
     int nb = 0;
-    if (!ok || cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rs_pass3<9, rs3_items(9), RS3_S, RS3_MINB, false, false>, RS_THREADS,
-                                                             (size_t)rs3_span(9) * 8) != cudaSuccess || nb <= 0) {
+    if (!ok || cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_rs_pass3<9, Rs3Cfg<9, false, false>::ITEMS, Rs3Cfg<9, false, false>::S, RS3_MINB, false, false>,
+                                                             RS_THREADS, (size_t)Rs3Cfg<9, false, false>::SPAN * 8) != cudaSuccess || nb <= 0) {
         cudaGetLastError();
         return -1;
     }

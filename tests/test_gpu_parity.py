@@ -345,6 +345,11 @@ def test_pose_batch_matches_single_draws(R):
         r.update_camera_pose(cam, True, pose)
         single = r.draw().cpu().numpy()
         assert np.array_equal(_bits(single), _bits(batch[i])), i
+    # and a frame of the batch against the oracle (not only the CUDA path against itself)
+    i = 3
+    ocam = O.make_camera(views[i], cam.get_project_matrix(), cam.get_htanfovxy_focal(), pos[i], 1.0, 3, g.sh_dim)
+    ref, fragile, _ = O.render(g, ocam, W, H, clamp_unorm=True, want_fragile=True)
+    _check_image(batch[i], ref, fragile, 3, "pose batch, 30k/480x270")
 
 
 def test_pipelined_readback_matches_synchronous(R):
