@@ -46,6 +46,14 @@ __device__ __forceinline__ uint32_t div_magic(uint32_t k, uint32_t w, uint32_t m
     return small ? __umulhi(k, magic) : k / w;
 }
 
+#ifdef GSR_DUP_TRACE  // development only: globaltimer stamps of the first chunk of every CTA (scripts/probe_dup_trace.py)
+__device__ unsigned long long g_dup_trace[2048 * 8];
+__device__ __forceinline__ unsigned long long dup_now() { unsigned long long v; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v)); return v; }
+#define DUP_T(i) do { if (threadIdx.x == 0 && dup_first && blockIdx.x < 2048) g_dup_trace[blockIdx.x * 8 + (i)] = dup_now(); } while (0)
+#else
+#define DUP_T(i) do { } while (0)
+#endif
+
 // KEYS64 = false: gid comes from sorted_gid, output key is the 32-bit tile id.
 // KEYS64 = true : gid is the running index, output key is (tile << 32) | depth bits.
 template <bool KEYS64>
@@ -57,7 +65,12 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
                                                           uint32_t* __restrict__ out_gid, unsigned n,
                                                           unsigned long long capacity, uint4* __restrict__ big_list,
                                                           uint32_t* __restrict__ big_count) {
+#ifdef GSR_DUP_TRACE
+    bool dup_first = true; unsigned long long dup_chunks = 0;
+    DUP_T(0);
+#endif
     pdl_wait();  // no global memory access before this (programmatic dependent launch)
+    DUP_T(1);
     __shared__ uint32_t s_warp[DUP_WARPS + 1];
     __shared__ uint32_t s_chunk;
     __shared__ unsigned long long s_prefix;
@@ -83,18 +96,31 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
         __syncthreads();
         const unsigned chunk = s_chunk;
         if (chunk >= n_chunks) break;
+        DUP_T(2);
+#ifdef GSR_DUP_TRACE
+        ++dup_chunks;
+#endif
         // ---- load: lane-strided inside the warp's 128 slots, so the gid reads coalesce
         const unsigned wbase = chunk * DUP_CHUNK + warp * (32 * DUP_ITEMS);
         uint32_t gid[DUP_ITEMS], cnt[DUP_ITEMS], rx[DUP_ITEMS], ry[DUP_ITEMS];
+        // (all index loads first, then all rectangle loads: a warp issues in order, and with each rectangle load
+        // right behind its index load the phase was DUP_ITEMS x 2 dependent round trips - 5.5 us per chunk in the
+        // globaltimer trace, scripts/probe_dup_trace.py)
 #pragma unroll
         for (int i = 0; i < DUP_ITEMS; ++i) {
             const unsigned r = wbase + i * 32 + lane;
-            gid[i] = 0; rx[i] = 0; ry[i] = 0;
-            if (r < n) {
-                gid[i] = KEYS64 ? r : __ldg(sorted_gid + r);
-                const uint2 tr = __ldg(sp.trect + gid[i]);
-                rx[i] = tr.x; ry[i] = tr.y;
-            }
+            gid[i] = KEYS64 ? r : ((r < n) ? __ldg(sorted_gid + r) : 0u);
+        }
+#pragma unroll
+        for (int i = 0; i < DUP_ITEMS; ++i) {
+            const unsigned r = wbase + i * 32 + lane;
+            uint2 tr = make_uint2(0u, 0u);
+            if (r < n) tr = __ldg(sp.trect + gid[i]);
+            rx[i] = tr.x; ry[i] = tr.y;
+        }
+#pragma unroll
+        for (int i = 0; i < DUP_ITEMS; ++i) {
+            if (KEYS64 && !(wbase + i * 32 + lane < n)) gid[i] = 0;
             cnt[i] = (rx[i] >> 16) * (ry[i] >> 16);
         }
         // ---- scan in slot order (slot = i * 32 + lane): per-round warp scans, then rounds, then warps
@@ -127,6 +153,7 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
         __syncthreads();
         const uint32_t chunk_total = s_warp[DUP_WARPS];
         const uint32_t wexcl = s_warp[warp];
+        DUP_T(3);
         // ---- chain the chunk total: warp 0 probes 32 predecessors per round trip (a one-thread walk left the
         // other 255 threads at the barrier for most of the kernel: ncu barrier stall 9 per issue)
         if (warp == 0) {
@@ -163,6 +190,7 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
             off[i] += wexcl;
         }
         __syncthreads();
+        DUP_T(4);
         const unsigned long long prefix = s_prefix;
         // large rectangles: (first output slot, rectangle, Gaussian) to the global list
 #pragma unroll
@@ -214,7 +242,14 @@ __global__ void __launch_bounds__(DUP_THREADS) k_duplicate(const FrameParams* __
             }
         }
         __syncthreads();
+        DUP_T(5);
+#ifdef GSR_DUP_TRACE
+        dup_first = false;
+#endif
     }
+#ifdef GSR_DUP_TRACE
+    if (threadIdx.x == 0 && blockIdx.x < 2048) { g_dup_trace[blockIdx.x * 8 + 6] = dup_now(); g_dup_trace[blockIdx.x * 8 + 7] = dup_chunks; }
+#endif
 }
 
 // Expands the large rectangles k_duplicate put on the global list: one warp per entry, entries dealt
@@ -424,6 +459,14 @@ __global__ void k_keys64_from_ranges(const int2* __restrict__ ranges, int n_tile
 int sm_count() { return sm_count_current(); }
 
 }  // namespace
+
+#ifdef GSR_DUP_TRACE
+extern "C" __attribute__((visibility("default"))) int gsr_debug_dup_trace(unsigned long long* out, long long n_words) {
+    if (n_words > 2048 * 8) n_words = 2048 * 8;
+    return (int)cudaMemcpyFromSymbol(out, g_dup_trace, (size_t)n_words * 8);
+}
+#endif
+
 
 void launch_duplicate_sorted(const FrameParams* fp, const uint32_t* sorted_gid, SplatBuffers sp, FrameCounters* counters,
                              uint32_t* chain_status, uint32_t* chain_ticket, uint32_t* out_tile, uint32_t* out_gid,
