@@ -526,6 +526,31 @@ def test_fast_and_generic_depth_sort_agree_bitwise(R):
         assert len(out[0][1]) > 0
 
 
+@pytest.mark.parametrize("n,eye_z", [(1_000_003, 60.0), (2_200_001, 60.0), (3_000_000, 60.0), (3_500_003, 60.0),
+                                     (2_158_000, 10.0), (444 * 4864 + 5, 80.0), (444 * 7680 + 31, 80.0)])
+def test_depth_sort_span_shapes_agree_with_the_generic_sort(R, n, eye_z):
+    """The compacting depth sort cuts the visible keys into one span per resident CTA: one sub-tile of 27 (first
+    pass) / 19 (other passes) keys per thread, a second sub-tile when more than 444 x 4864 Gaussians are visible, a second
+    wave above 444 x 7680 (B200: 148 SMs x 3 CTAs).  With the camera far away every Gaussian is visible, so N picks the
+    shape: ragged last warps, exactly full sub-tiles, the sub-tile and wave boundaries +- a few keys.  Instance list and
+    ranges bit-identical to the generic sort (histogram kernel, four 8-bit passes over all N)."""
+    g = scenes.synthetic_gaussians(n, seed=37)
+    W, H = 640, 360
+    out = []
+    for fast in (1, 0):
+        r, _ = _setup(R, g, W, H, eye=(0.0, 0.0, eye_z), mod=0, debug=False)
+        r.tune(_gsr.GSR_TUNE_FUSED_DEPTH_HIST, fast)
+        r.draw()
+        st = r.stats()
+        out.append((r.debug_fetch(_gsr.GSR_DBG_INST_VALS, np.uint32), r.debug_fetch(_gsr.GSR_DBG_RANGES, np.int32),
+                    np.array([st.n_visible, st.n_instances])))
+        del r
+    assert out[0][2][0] > 0.6 * n or eye_z < 20.0
+    _report(f"[parity] depth-sort shapes: N {n}, visible {int(out[0][2][0])}, instances {int(out[0][2][1])}")
+    for a_, b_ in zip(out[0], out[1]):
+        assert np.array_equal(a_, b_)
+
+
 @pytest.mark.parametrize("W,H,tile", [(483, 271, 32), (484, 270, 16), (96, 64, 32), (50, 30, 32)])
 def test_rgb8_from_the_blend_kernel_matches_the_pack_kernel(R, W, H, tile):
     """gsr_render_rgb8_host_async takes the RGB8 frame from the blend kernel's epilogue (aligned words out of
