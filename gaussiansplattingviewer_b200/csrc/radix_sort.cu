@@ -1,18 +1,21 @@
 // K3 — hand-written onesweep LSB radix sort (key/value pairs) for sm_100a.
 //
 // Replaces the torch / cupy / numpy argsort of /root/reference/renderer_ogl.py:10-53 and the CUB
-// DeviceRadixSort inside diff_gaussian_rasterization.  Stable, 8-bit digits, 32- or 64-bit keys,
+// DeviceRadixSort inside diff_gaussian_rasterization.  Stable, digits of 5 to 9 bits, 32- or 64-bit keys,
 // 32-bit values.
 //
-//   k_rs_hist : ONE read of the keys builds the digit histograms of ALL passes (shared-memory
-//               histograms, one global atomic per bin per CTA) and clears the first look-back buffer.
-//   k_rs_pass : one kernel per digit.  Persistent CTAs take tiles in ticket order; each tile is ranked
-//               with warp match_any + per-warp digit counters, its per-digit counts are chained to
-//               the previous tiles with decoupled look-back (single 32-bit status word per
-//               (tile, digit): 2 flag bits + 30 count bits), and keys/values are scattered through
-//               shared memory so global stores are contiguous per digit run.  No global memory
-//               round trip between "count" and "scatter": keys are read once and written once per
-//               pass (the onesweep property).
+//   k_rs_hist  : ONE read of the keys builds the digit histograms of ALL passes (shared-memory
+//                histograms, one global atomic per bin per CTA) and clears the first look-back buffer.  The
+//                frame's two sorts do not run it: their histograms come from k_preprocess / k_tile_scan.
+//   k_rs_pass3 : one kernel per digit of a 32-bit-key sort.  Persistent CTAs take equal spans of keys in ticket
+//                order; a span is ranked in one or two sub-tiles (ballot matching + per-warp digit counters), parked
+//                tile-sorted in shared memory, its per-digit counts are chained to the spans in front through
+//                self-validating status words (AGG per tile, GROUP per 16 tiles, CKPT per group boundary:
+//                tile_prefix / tile_prefix_thread), and keys/values leave in contiguous runs per digit.  Keys are read
+//                once and written once per pass (the onesweep property).  The first pass of the frame's depth sort
+//                also compacts (DROP: culled Gaussians have no key) and rebases the keys to 27 bits.
+//   k_rs_pass  : the same for 64-bit keys (GSR_FLAG_KEYS64 cross-check path): tiles of 12 keys per thread, decoupled
+//                look-back over one status word per (tile, digit).
 //
 // Item counts may live on the device (n_dev): grids are sized for the SM count, not for n, so the
 // same launch (and the same captured CUDA graph) serves any n up to the buffer capacity.
