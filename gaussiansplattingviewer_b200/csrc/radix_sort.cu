@@ -309,7 +309,8 @@ __device__ unsigned long long g_rs_trace2[5 * 1024 * 10];
 __device__ int g_rs_slot_dummy;
 #define RS_P(i, val) do { if (threadIdx.x == 0 && tr_on && blockIdx.x < 1024) g_rs_trace2[(tr_slot * 1024 + blockIdx.x) * 10 + (i)] = (val); } while (0)
 __device__ __forceinline__ unsigned long long rs_now() { unsigned long long v; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(v)); return v; }
-#define RS_T(i) do { if (threadIdx.x == 0 && rs_first && blockIdx.x < 1024) g_rs_trace[(rs_slot * 1024 + blockIdx.x) * 10 + (i)] = rs_now(); } while (0)
+__device__ unsigned long long g_rs_acc[5 * 1024 * 8];  // per CTA, summed over ALL its tiles: ticket, clear, sub-tile 0, sub-tile 1, prefix, scatter; tiles
+#define RS_T(i) do { if (threadIdx.x == 0) { const unsigned long long now_ = rs_now(); if ((i) >= 2) { rs_acc[(i) - 2] += now_ - rs_prev; } rs_prev = now_; if (rs_first && blockIdx.x < 1024) g_rs_trace[(rs_slot * 1024 + blockIdx.x) * 10 + (i)] = now_; } } while (0)
 #else
 #define RS_T(i) do { } while (0)
 #define RS_P(i, val) do { } while (0)
@@ -756,6 +757,7 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
 #ifdef GSR_RS_TRACE
     const int rs_slot = (bits == 9) ? shift / 9 : (shift > 0 ? 4 : 3);
     bool rs_first = true;
+    unsigned long long rs_prev = 0, rs_acc[6] = {0, 0, 0, 0, 0, 0}, rs_tiles = 0;
     RS_T(0);
 #endif
     pdl_wait();  // resident behind the previous pass; nothing of global memory is touched before this
@@ -1016,9 +1018,16 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
         __syncthreads();  // staging and s_bin_base are rewritten by the next super-tile
         RS_T(7);
 #ifdef GSR_RS_TRACE
-        rs_first = false;
+        rs_first = false; ++rs_tiles;
 #endif
     }
+#ifdef GSR_RS_TRACE
+    if (threadIdx.x == 0 && blockIdx.x < 1024) {
+        for (int i = 0; i < 6; ++i) g_rs_acc[(rs_slot * 1024 + blockIdx.x) * 8 + i] = rs_acc[i];
+        g_rs_acc[(rs_slot * 1024 + blockIdx.x) * 8 + 6] = rs_tiles;
+        g_rs_acc[(rs_slot * 1024 + blockIdx.x) * 8 + 7] = rs_now();
+    }
+#endif
 }
 
 #ifdef GSR_RS_TRACE
@@ -1026,6 +1035,10 @@ __global__ void __launch_bounds__(RS_THREADS, MINB) k_rs_pass3(const uint32_t* _
 extern "C" __attribute__((visibility("default"))) int gsr_debug_rs_trace(unsigned long long* out, long long n_words) {
     if (n_words > 5 * 1024 * 10) n_words = 5 * 1024 * 10;
     return (int)cudaMemcpyFromSymbol(out, g_rs_trace, (size_t)n_words * 8);
+}
+extern "C" __attribute__((visibility("default"))) int gsr_debug_rs_acc(unsigned long long* out, long long n_words) {
+    if (n_words > 5 * 1024 * 8) n_words = 5 * 1024 * 8;
+    return (int)cudaMemcpyFromSymbol(out, g_rs_acc, (size_t)n_words * 8);
 }
 extern "C" __attribute__((visibility("default"))) int gsr_debug_rs_trace2(unsigned long long* out, long long n_words) {
     if (n_words > 5 * 1024 * 10) n_words = 5 * 1024 * 10;
