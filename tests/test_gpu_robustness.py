@@ -157,3 +157,32 @@ def test_graph_replay_is_bit_identical_to_direct_launches(R):
     for i, (x, y) in enumerate(zip(a, b)):
         assert x.shape == y.shape and np.array_equal(x.view(np.uint8), y.view(np.uint8)), i
     assert not np.array_equal(a[0], a[1])
+
+
+def test_resident_scene_buffers_filled_in_place(R):
+    """gsr_alloc_gaussians + gsr_scene_buffer: the receiving side of a scene broadcast
+    (pose_shard.broadcast_scene_resident, bench.py at N > 1).  A handle whose resident planes are filled in place from
+    another handle's planes (what dist.broadcast does across ranks) renders the same bits as one fed through
+    update_gaussian_data; the planes alias the library's memory (no copy)."""
+    g = scenes.synthetic_gaussians(50_000, seed=45)
+    W, H = 480, 270
+    src, cam, pose = _renderer(R, g, W, H)
+    want = src.draw().cpu().numpy().copy()
+    dst = R(W, H)
+    dst.alloc_gaussians(len(g), g.sh_dim)
+    a, b = src.scene_buffers(), dst.scene_buffers()
+    assert [tuple(t.shape) for t in a] == [(len(g), 3), (len(g), 4), (len(g), 4), (len(g), g.sh_dim)]
+    assert [tuple(t.shape) for t in b] == [tuple(t.shape) for t in a]
+    assert np.array_equal(a[0].cpu().numpy(), g.xyz)                 # the planes ARE the scene
+    assert np.array_equal(a[2].cpu().numpy()[:, 3:4], g.opacity)
+    for ta, tb in zip(a, b):
+        assert ta.data_ptr() != tb.data_ptr()
+        tb.copy_(ta)                                                 # in place, like a broadcast
+    dst.set_render_mod(3)
+    dst.update_camera_intrin(cam)
+    dst.update_camera_pose(cam, True, pose)
+    got = dst.draw().cpu().numpy()
+    assert np.array_equal(_bits(got), _bits(want))
+    assert dst.stats().n_gaussians == len(g)
+    again = dst.scene_buffers()
+    assert [t.data_ptr() for t in again] == [t.data_ptr() for t in b]
